@@ -1,0 +1,90 @@
+// Host-side data preparation for the path tracer (C++17, no CUDA, no OpenCL).
+//
+// This is the "L0" layer of the reference re-written for Linux: config.json
+// loading, OBJ/MTL scene loading with the reference's material classification, camera basis,
+// the LBVH build whose node array is bit-identical to the reference's BVH/hlbvh.cpp, and the
+// .hdr/.png writers.  Everything here feeds the C ABI in include/mcpt.h with the PODs of
+// include/mcpt_types.h.
+#pragma once
+
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "mcpt_types.h"
+
+namespace mcpt::host {
+
+// ------------------------------------------------------------------ JSON (+ '#' comments)
+// Minimal DOM sufficient for config.json.  The reference patches nlohmann/json's lexer to skip
+// `# ... EOL` comments (json.hpp:3037-3043); this parser accepts the same superset.
+struct Json {
+	enum Kind { Null, Bool, Number, String, Array, Object } kind = Null;
+	bool b = false;
+	double num = 0.0;
+	std::string str;
+	std::vector<Json> arr;
+	std::vector<std::pair<std::string, Json>> obj;   // insertion order kept
+
+	bool has(const std::string& key) const;
+	const Json& at(const std::string& key) const;    // throws std::runtime_error when absent
+	const Json& at(size_t i) const;
+	double number() const;                           // throws unless Number
+	const std::string& string() const;               // throws unless String
+	bool boolean() const;                            // Bool, or Number != 0
+	size_t size() const { return kind == Array ? arr.size() : obj.size(); }
+	static Json parse(const std::string& text);      // throws std::runtime_error with offset
+};
+
+// ------------------------------------------------------------------ config.json
+// Same keys as the reference (config.cpp:70-125).  Kernel-path / platform keys
+// are accepted and ignored.
+struct RenderConfig {
+	std::string bvhtype = "hlbvh";   // "hlbvh" | "treelet" | "treeletGPU" (treated as "treelet")
+	int width = 0, height = 0;
+	std::string directory, objname;
+	int maxdepth = 0;
+	int attempt = 0;                 // samples per pixel
+	bool opencl = true;              // accepted; false makes the reference throw "Not Implemented"
+	bool testbvh = false, testall = false;
+	bool has_camera = false;
+	Json camera;                     // position / lookat / up / fov / resolution
+	int res_x = 0, res_y = 0;        // camera.resolution (ray count uses this, raygeneration.cpp:51-56)
+};
+RenderConfig load_config(const std::string& path, int configid_override = -1);
+RenderConfig config_from_json(const Json& root, int configid_override = -1);
+
+// ------------------------------------------------------------------ camera
+// auxiliary.cpp:20-71 — identical float/double operation order.
+mcpt_camera parse_camera(const Json& cam);
+
+// ------------------------------------------------------------------ scene loading
+struct Scene {
+	std::vector<mcpt_triangle> triangles;   // normal + material id filled (scenebuild.cpp:58-62)
+	std::vector<mcpt_material> materials;   // thirdpartywrapper.cpp:65-97 classification
+	std::vector<int> material_ids;          // per triangle
+	std::vector<std::string> material_names;
+};
+// with_normals=false leaves Triangle::normal/material_id zero exactly like loadObject() does.
+Scene load_object(const std::string& directory, const std::string& objname, bool with_normals = true);
+
+// ------------------------------------------------------------------ BVH
+// LBVH (BVH/hlbvh.cpp:92-200): 30-bit Morton of AABB centroids, stable sort, split at the
+// highest differing bit, node numbering internal 0..N-2 / leaves N-1..2N-2.  memcmp-equal to the
+// reference's node array for the same triangle list.
+std::vector<mcpt_bvh_node> build_hlbvh(const std::vector<mcpt_triangle>& tris);
+// Karras-2013 treelet restructuring on the CPU (BVH/treeletBVH.cpp:30-365), same slots.
+std::vector<mcpt_bvh_node> optimize_treelet(const std::vector<mcpt_bvh_node>& nodes);
+// SAH cost as in bvhtest.cpp:104-115 (check only).
+double sah_cost(const std::vector<mcpt_bvh_node>& nodes);
+
+// ------------------------------------------------------------------ image output
+// Radiance RGBE, vertical flip, RLE scanlines as stb_image_write 1.13 emits them
+// (thirdpartywrapper.cpp:14-23).  rgba = W*H float4, row 0 = image bottom.
+bool write_hdr(const std::string& path, int w, int h, const float* rgba);
+// 8-bit RGB PNG of pow(clamp(c),1/2.2) (testkernel.cl:9-14 display transform), same flip.
+bool write_png(const std::string& path, int w, int h, const float* rgba);
+
+}  // namespace mcpt::host

@@ -1,0 +1,108 @@
+// C exports of the host data-preparation layer (libmcpt_host.so; no CUDA dependency).
+// Declared in include/mcpt_host.h.  Status convention as the device ABI: 0 = OK, negative = error,
+// text via mcpt_host_last_error().
+#include <cstdlib>
+#include <cstring>
+
+#include "host.hpp"
+#include "mcpt_host.h"
+
+using namespace mcpt::host;
+
+namespace {
+thread_local std::string g_err;
+template <class F>
+int guarded(F&& f) {
+	try { return f(); }
+	catch (const std::exception& e) { g_err = e.what(); return -1; }
+	catch (...) { g_err = "unknown error"; return -1; }
+}
+template <class T>
+T* dup(const std::vector<T>& v) {
+	T* p = static_cast<T*>(std::malloc(v.size() * sizeof(T) + 1));
+	if (!v.empty()) std::memcpy(p, v.data(), v.size() * sizeof(T));
+	return p;
+}
+}  // namespace
+
+extern "C" {
+
+const char* mcpt_host_last_error(void) { return g_err.c_str(); }
+void mcpt_host_free(void* p) { std::free(p); }
+
+int mcpt_host_load_object(const char* directory, const char* objname, int with_normals,
+                          mcpt_triangle** tris, int* ntris, mcpt_material** mats, int* nmats,
+                          int** material_ids) {
+	return guarded([&] {
+		Scene s = load_object(directory, objname, with_normals != 0);
+		*ntris = int(s.triangles.size());
+		*nmats = int(s.materials.size());
+		*tris = dup(s.triangles);
+		*mats = dup(s.materials);
+		*material_ids = dup(s.material_ids);
+		return 0;
+	});
+}
+
+int mcpt_host_build_bvh(const mcpt_triangle* tris, int n, const char* bvhtype, mcpt_bvh_node* out_nodes) {
+	return guarded([&] {
+		std::vector<mcpt_triangle> t(tris, tris + n);
+		std::vector<mcpt_bvh_node> nodes = build_hlbvh(t);
+		std::string kind = bvhtype ? bvhtype : "hlbvh";
+		if (kind == "treelet" || kind == "treeletGPU") nodes = optimize_treelet(nodes);
+		else if (kind != "hlbvh") throw std::runtime_error("BVH Not Implemented");   // scenebuild.cpp:76
+		std::memcpy(out_nodes, nodes.data(), nodes.size() * sizeof(mcpt_bvh_node));
+		return int(nodes.size());
+	});
+}
+
+int mcpt_host_treelet(const mcpt_bvh_node* nodes_in, int nn, mcpt_bvh_node* out_nodes) {
+	return guarded([&] {
+		std::vector<mcpt_bvh_node> v(nodes_in, nodes_in + nn);
+		v = optimize_treelet(v);
+		std::memcpy(out_nodes, v.data(), v.size() * sizeof(mcpt_bvh_node));
+		return int(v.size());
+	});
+}
+
+double mcpt_host_sah(const mcpt_bvh_node* nodes, int nn) {
+	std::vector<mcpt_bvh_node> v(nodes, nodes + nn);
+	return sah_cost(v);
+}
+
+int mcpt_host_parse_camera(const char* json_text, mcpt_camera* out) {
+	return guarded([&] {
+		*out = parse_camera(Json::parse(json_text));
+		return 0;
+	});
+}
+
+int mcpt_host_load_config(const char* path, int configid, mcpt_host_config* out) {
+	return guarded([&] {
+		RenderConfig c = load_config(path, configid);
+		std::memset(out, 0, sizeof(*out));
+		auto put = [](char* dst, size_t cap, const std::string& s) {
+			std::strncpy(dst, s.c_str(), cap - 1);
+			dst[cap - 1] = 0;
+		};
+		put(out->bvhtype, sizeof(out->bvhtype), c.bvhtype);
+		put(out->directory, sizeof(out->directory), c.directory);
+		put(out->objname, sizeof(out->objname), c.objname);
+		out->width = c.width; out->height = c.height;
+		out->maxdepth = c.maxdepth; out->attempt = c.attempt;
+		out->opencl = c.opencl; out->testbvh = c.testbvh; out->testall = c.testall;
+		out->has_camera = c.has_camera;
+		out->res_x = c.res_x; out->res_y = c.res_y;
+		if (c.has_camera) out->camera = parse_camera(c.camera);
+		return 0;
+	});
+}
+
+int mcpt_host_write_hdr(const char* path, int w, int h, const float* rgba) {
+	return write_hdr(path, w, h, rgba) ? 0 : -1;
+}
+int mcpt_host_write_png(const char* path, int w, int h, const float* rgba) {
+	return write_png(path, w, h, rgba) ? 0 : -1;
+}
+
+}  // extern "C"
