@@ -1,0 +1,127 @@
+"""ctypes binding of libmcpt_host.so — the host data-preparation layer (include/mcpt_host.h).
+
+Mirrors the reference's L0 entry points: ThirdPartyWrapper::loadObject (thirdpartywrapper.cpp:25-99),
+HLBVH<CPU> (BVH/hlbvh.cpp:92-200), Auxiliary::parseCamera (auxiliary.cpp:20-71), Config
+(config.cpp:70-125) and outputPicture (thirdpartywrapper.cpp:14-23).
+"""
+import ctypes
+import json
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import types as T
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class HostConfigStruct(ctypes.Structure):
+    _fields_ = [("bvhtype", ctypes.c_char * 32), ("directory", ctypes.c_char * 512),
+                ("objname", ctypes.c_char * 256), ("width", ctypes.c_int), ("height", ctypes.c_int),
+                ("maxdepth", ctypes.c_int), ("attempt", ctypes.c_int), ("opencl", ctypes.c_int),
+                ("testbvh", ctypes.c_int), ("testall", ctypes.c_int), ("has_camera", ctypes.c_int),
+                ("res_x", ctypes.c_int), ("res_y", ctypes.c_int), ("camera", ctypes.c_uint8 * 80)]
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_PKG_DIR, "libmcpt_host.so")
+        if not os.path.exists(path):
+            raise RuntimeError("libmcpt_host.so is not built - run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = ctypes.CDLL(path)
+        L.mcpt_host_last_error.restype = ctypes.c_char_p
+        L.mcpt_host_sah.restype = ctypes.c_double
+        _LIB = L
+    return _LIB
+
+
+def _check(rc):
+    if rc < 0:
+        raise RuntimeError("mcpt_host: " + lib().mcpt_host_last_error().decode())
+    return rc
+
+
+@dataclass
+class Scene:
+    triangles: np.ndarray      # T.TRIANGLE
+    materials: np.ndarray      # T.MATERIAL
+    material_ids: np.ndarray   # int32 per triangle
+
+
+def load_object(directory, objname, with_normals=True):
+    L = lib()
+    tr, mt = ctypes.c_void_p(), ctypes.c_void_p()
+    ids = ctypes.POINTER(ctypes.c_int)()
+    nt, nm = ctypes.c_int(), ctypes.c_int()
+    _check(L.mcpt_host_load_object(directory.encode(), objname.encode(), int(with_normals),
+                                   ctypes.byref(tr), ctypes.byref(nt), ctypes.byref(mt), ctypes.byref(nm),
+                                   ctypes.byref(ids)))
+    try:
+        tris = np.frombuffer(ctypes.string_at(tr, nt.value * 64), dtype=T.TRIANGLE).copy()
+        mats = np.frombuffer(ctypes.string_at(mt, nm.value * 48), dtype=T.MATERIAL).copy()
+        mids = np.frombuffer(ctypes.string_at(ids, nt.value * 4), dtype=np.int32).copy()
+    finally:
+        L.mcpt_host_free(tr); L.mcpt_host_free(mt); L.mcpt_host_free(ids)
+    return Scene(tris, mats, mids)
+
+
+def build_bvh(triangles, bvhtype="hlbvh"):
+    tris = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
+    nodes = np.zeros(2 * len(tris) - 1, dtype=T.BVH_NODE)
+    n = _check(lib().mcpt_host_build_bvh(tris.ctypes.data_as(ctypes.c_void_p), len(tris), bvhtype.encode(),
+                                         nodes.ctypes.data_as(ctypes.c_void_p)))
+    assert n == len(nodes)
+    return nodes
+
+
+def treelet(nodes):
+    src = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    out = np.zeros_like(src)
+    _check(lib().mcpt_host_treelet(src.ctypes.data_as(ctypes.c_void_p), len(src), out.ctypes.data_as(ctypes.c_void_p)))
+    return out
+
+
+def sah(nodes):
+    src = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    return lib().mcpt_host_sah(src.ctypes.data_as(ctypes.c_void_p), len(src))
+
+
+def parse_camera(cam):
+    """cam: dict with position/lookat/up/fov (the config.json "camera" object) or its JSON text."""
+    text = cam if isinstance(cam, str) else json.dumps(cam)
+    out = np.zeros(1, dtype=T.CAMERA)
+    _check(lib().mcpt_host_parse_camera(text.encode(), out.ctypes.data_as(ctypes.c_void_p)))
+    return out
+
+
+def load_config(path, configid=-1):
+    s = HostConfigStruct()
+    _check(lib().mcpt_host_load_config(path.encode(), configid, ctypes.byref(s)))
+    d = {k: getattr(s, k) for k in ("width", "height", "maxdepth", "attempt", "opencl", "testbvh", "testall",
+                                    "has_camera", "res_x", "res_y")}
+    d.update(bvhtype=s.bvhtype.decode(), directory=s.directory.decode(), objname=s.objname.decode())
+    d["camera"] = np.frombuffer(bytes(s.camera), dtype=T.CAMERA).copy()
+    return d
+
+
+def write_hdr(path, rgba):
+    img = np.ascontiguousarray(rgba, dtype=np.float32)
+    h, w = img.shape[:2]
+    _check(lib().mcpt_host_write_hdr(path.encode(), w, h, img.ctypes.data_as(ctypes.POINTER(ctypes.c_float))))
+
+
+def write_png(path, rgba):
+    img = np.ascontiguousarray(rgba, dtype=np.float32)
+    h, w = img.shape[:2]
+    _check(lib().mcpt_host_write_png(path.encode(), w, h, img.ctypes.data_as(ctypes.POINTER(ctypes.c_float))))
+
+
+# Scene cameras of the three course scenes (Scene/README.md:20-61, config.json:20-26,47-53,75-81).
+CAMERAS = {
+    "cbox": {"position": [278, 273, -800], "lookat": [278, 273, -799], "up": [0, 1, 0], "fov": 39.3077},
+    "veach_mis": {"position": [0, 2, 15], "lookat": [0, -2, 2.5], "up": [0, 1, 0], "fov": 28},
+    "diningroom": {"position": [-0.5, 3, 5.5], "lookat": [-0.5, 2, 0], "up": [0, 1, 0], "fov": 60},
+}
