@@ -1,0 +1,131 @@
+/* mcpt.h — C ABI of the CUDA hot path (libmcpt_cuda.so, sm_100a).
+ *
+ * This library stands where the reference's OpenCL layer stands: OpenCLApp.{h,cpp} (frame
+ * orchestrator), oclbasic.{h,cpp} (device runtime) and kernels/*.cl.  Every entry point names the
+ * reference interface it replaces.  Records crossing the boundary are the PODs of mcpt_types.h,
+ * byte-identical to objdef.h:21-99, so a reference-side caller passes its std::vector storage
+ * unchanged.  No exceptions cross the ABI: 0 = OK, negative = error, text via mcpt_last_error().
+ * A context is thread-compatible (one caller at a time), there are no globals, and there is NO
+ * CPU fallback: every call fails with MCPT_ERR_CUDA when no sm_100 device is usable.
+ *
+ *   reference                                              replacement
+ *   OpenCL::init()              OpenCLApp.cpp:36-55         mcpt_create + mcpt_upload_scene + mcpt_set_camera
+ *   SceneBuild::buildScene()    scenebuild.cpp:50-101,149   mcpt_upload_scene
+ *   RayGeneration::init()       raygeneration.cpp:41-67     mcpt_set_camera
+ *   RayGeneration::generateRay  raygeneration.cpp:29-35     mcpt_generate_rays      (kernel generateRay, rayGenerator.cl:1-31)
+ *   SceneBase::intersect        scenebuild.cpp:103-133      mcpt_intersect          (kernel intersectRays, intersect.cl:1-28)
+ *   SceneBase::shade            scenebuild.cpp:136-145      mcpt_shade              (kernel shade, shade.cl:75-206)
+ *   ColorOut::outputColorCL     colorout.cpp:40-73          mcpt_accumulate + mcpt_display (history.cl:3-28, testkernel.cl:1-15)
+ *   OpenCL::update()            OpenCLApp.cpp:57-82         mcpt_frame (stage kernels, one sample) / mcpt_render (fused wavefront)
+ *   OpenCLBasic::readBuffer     oclbasic.cpp:220-222        mcpt_read_*
+ *   OpenCLBasic::writeBuffer    oclbasic.cpp:224-226        mcpt_write_*
+ *   outputPicture's readback    thirdpartywrapper.cpp:14-23 mcpt_read_history (then mcpt_host_write_hdr)
+ */
+#ifndef MCPT_H
+#define MCPT_H
+
+#include "mcpt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mcpt_ctx mcpt_ctx;
+
+enum {
+	MCPT_OK = 0,
+	MCPT_ERR_ARG = -1,      /* bad argument / call order (the reference asserts or throws a C string) */
+	MCPT_ERR_CUDA = -2,     /* CUDA runtime error, no device, or wrong architecture */
+	MCPT_ERR_STATE = -3     /* scene or camera not uploaded yet */
+};
+
+/* Traversal algorithms.  Both return the reference's closest hit (SURVEY.md §8c definition). */
+enum {
+	MCPT_TRAVERSAL_REFERENCE = 0,  /* objdef.h:240-275 as written: 64 B nodes, one box per visit, no pruning,
+	                                   literal 4x4-cofactor arithmetic order; also reproduces Hit.triangleID (F7) */
+	MCPT_TRAVERSAL_FAST = 1        /* same canonical left-first leaf order, two-box nodes, conservative inner
+	                                   tests, exact leaf-box + triangle arithmetic, margin-guarded pruning */
+};
+
+typedef struct mcpt_params {
+	int width, height;        /* config "width"/"height" == camera.resolution */
+	int max_depth;            /* config "maxdepth"  (-D MAX_DEPTH,   scenebuild.cpp:163) */
+	int max_attempt;          /* config "attempt"   (-D MAX_ATTEMPT, colorout.cpp:35)    */
+	int device;               /* CUDA device ordinal (reference: devices[0], oclbasic.cpp:102) */
+	int seed_mode;            /* 0: one LCG stream per pixel, seeded once (shade.cl:101, reference behaviour)
+	                             1: stream re-seeded for every (pixel, sample index): order independent, used
+	                                for sample-index sharding across GPUs */
+	uint32_t run_seed;        /* replaces srand(time(NULL)) (scenebuild.cpp:116-119) */
+	int samples_in_flight;    /* seed_mode 1: samples per wave of mcpt_render (0 = automatic); mode 0 uses 1 */
+	float tmin;               /* host EPSILON 0.001f (oclbasic.h:193, scenebuild.cpp:125); 0 selects it */
+	int traversal;            /* MCPT_TRAVERSAL_* used by mcpt_render / mcpt_trace (stage calls take their own) */
+	int reserved[6];
+} mcpt_params;
+
+typedef struct mcpt_stats {
+	uint64_t rays_traced;     /* live rays that entered an intersect stage since create/reset (Mrays/s numerator) */
+	uint64_t paths;           /* pixel samples finished by mcpt_render / mcpt_frame (Mpaths/s numerator) */
+	uint64_t kernel_launches; /* CUDA kernels launched by this context */
+	uint64_t nodes_fetched;   /* only filled by mcpt_trace_count */
+	uint64_t tris_fetched;
+} mcpt_stats;
+
+const char* mcpt_last_error(void);
+int mcpt_abi_version(void);
+
+mcpt_ctx* mcpt_create(const mcpt_params* params);          /* NULL on error */
+void mcpt_destroy(mcpt_ctx* ctx);
+void* mcpt_stream(mcpt_ctx* ctx);                           /* the cudaStream_t every call of ctx is ordered on */
+int mcpt_synchronize(mcpt_ctx* ctx);
+
+/* Host arrays are borrowed for the call and copied.  nodes = the canonical BVHNode[2n-1] of
+ * mcpt_host_build_bvh (reference layout); the device traversal layout is derived here. */
+int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                      const mcpt_bvh_node* nodes, int nnodes);
+int mcpt_set_camera(mcpt_ctx* ctx, const mcpt_camera* cam);
+
+/* ---- stage level: one call = one reference kernel over the W*H work items (reference buffer layouts) ---- */
+int mcpt_generate_rays(mcpt_ctx* ctx);                      /* rays <- camera */
+int mcpt_reset_color(mcpt_ctx* ctx);                        /* colorBuffer <- (1,1,1,1), OpenCLApp.cpp:63 */
+int mcpt_intersect(mcpt_ctx* ctx, int traversal);           /* hits <- rays; dead rays untouched */
+int mcpt_shade(mcpt_ctx* ctx);                              /* rays, color, seeds updated in place */
+int mcpt_accumulate(mcpt_ctx* ctx);                         /* history.cl: hist/count updated, color <- running mean */
+int mcpt_display(mcpt_ctx* ctx, int from_history, float* host_rgba);  /* testkernel.cl: pow(c,1/2.2), w=0 */
+int mcpt_frame(mcpt_ctx* ctx);                              /* OpenCL::update(): reset, generate, maxdepth x (intersect, shade), accumulate */
+
+/* ---- fused wavefront path (the product): spp more samples for every pixel, all on the device ---- */
+int mcpt_render(mcpt_ctx* ctx, int spp);
+int mcpt_render_async(mcpt_ctx* ctx, int spp);              /* enqueue only; mcpt_synchronize to wait */
+int mcpt_set_first_sample(mcpt_ctx* ctx, uint32_t first);   /* seed_mode 1: global index of the next sample */
+int mcpt_reset_accumulation(mcpt_ctx* ctx);                 /* hist, count, sums <- 0; seeds re-derived */
+
+/* ---- buffer I/O (blocking, like readBuffer/writeBuffer with CL_TRUE) ---- */
+int mcpt_read_rays(mcpt_ctx* ctx, mcpt_ray* dst);
+int mcpt_write_rays(mcpt_ctx* ctx, const mcpt_ray* src);
+int mcpt_read_hits(mcpt_ctx* ctx, mcpt_hit* dst, int32_t* closest /* may be NULL */);
+int mcpt_write_hits(mcpt_ctx* ctx, const mcpt_hit* src);
+int mcpt_read_color(mcpt_ctx* ctx, float* rgba);
+int mcpt_write_color(mcpt_ctx* ctx, const float* rgba);
+int mcpt_read_seeds(mcpt_ctx* ctx, uint32_t* dst);
+int mcpt_write_seeds(mcpt_ctx* ctx, const uint32_t* src);
+int mcpt_read_history(mcpt_ctx* ctx, float* hist_rgba, int32_t* counts /* may be NULL */);
+/* 7 planes of W*H doubles: sum r,g,b; sum of squares r,g,b; counted (non-zero, capped) samples */
+int mcpt_read_sums(mcpt_ctx* ctx, double* dst);
+/* Accumulate the sums in caller-owned DEVICE memory (7*W*H doubles, e.g. the NCCL reduce buffer); NULL = own. */
+int mcpt_bind_sums(mcpt_ctx* ctx, double* device_ptr);
+
+/* ---- intersection microbench / ad-hoc queries against the uploaded scene ---- */
+/* host buffers: copies in, traces n rays, copies out (hits 48 B each; closest may be NULL) */
+int mcpt_trace(mcpt_ctx* ctx, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_t* closest, int traversal);
+/* device-resident buffers, enqueued on mcpt_stream(ctx), no synchronisation */
+int mcpt_trace_device(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal);
+/* instrumented build of the same kernel: counts node and triangle records fetched (device buffers) */
+int mcpt_trace_count(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, int traversal);
+
+int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
+int mcpt_reset_stats(mcpt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCPT_H */

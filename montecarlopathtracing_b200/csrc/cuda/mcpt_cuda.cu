@@ -1,0 +1,575 @@
+// libmcpt_cuda.so — context management and the C ABI of include/mcpt.h (sm_100a only, no CPU fallback).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "mcpt.h"
+#include "mcpt_kernels.cuh"
+
+using namespace mcpt;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+	g_err = msg;
+	return code;
+}
+
+#define CU(call)                                                                                       \
+	do {                                                                                               \
+		cudaError_t e_ = (call);                                                                       \
+		if (e_ != cudaSuccess)                                                                         \
+			return fail(MCPT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));            \
+	} while (0)
+
+template <class T>
+struct DevBuf {
+	T* p = nullptr;
+	size_t n = 0;
+	cudaError_t alloc(size_t count) {
+		release();
+		n = count;
+		return count ? cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T)) : cudaSuccess;
+	}
+	void release() {
+		if (p) cudaFree(p);
+		p = nullptr;
+		n = 0;
+	}
+};
+
+}  // namespace
+
+struct mcpt_ctx {
+	mcpt_params prm{};
+	cudaStream_t stream = nullptr;
+	int npix = 0;
+	bool have_scene = false, have_camera = false;
+	bool force_reference = false;     // node array violates box containment: monotonicity argument void
+	CameraDev cam{};
+	SceneDev scene{};
+	// scene
+	DevBuf<mcpt_bvh_node> nodes_ref;
+	DevBuf<mcpt_triangle> tris_ref;
+	DevBuf<DNode> nodes;
+	DevBuf<DTri> tris;
+	DevBuf<mcpt_material> mats;
+	DevBuf<float2> cs_table;
+	// reference-layout frame buffers (stage path)
+	DevBuf<mcpt_ray> rays;
+	DevBuf<mcpt_hit> hits;
+	DevBuf<int32_t> closest;
+	DevBuf<float4> color, hist, display;
+	DevBuf<uint32_t> seeds;
+	DevBuf<int32_t> counts;
+	DevBuf<double> sums_own;
+	double* sums = nullptr;
+	// wavefront path
+	int wave_samples = 0;             // allocated samples per wave
+	DevBuf<float4> od[2], dp[2], cs[2], sample_out;
+	DevBuf<uint32_t> qcount, first_sample;
+	DevBuf<unsigned long long> counters;   // 0 nodes, 1 tris, 2 live rays (stage path), 3 rays (wave), 4 paths (wave)
+	// trace scratch
+	DevBuf<mcpt_ray> t_rays;
+	DevBuf<mcpt_hit> t_hits;
+	DevBuf<int32_t> t_closest;
+	uint64_t launches = 0;
+	uint64_t stage_paths = 0;
+
+	~mcpt_ctx() {
+		if (stream) cudaStreamDestroy(stream);
+	}
+	FrameDev frame() {
+		return FrameDev{rays.p, hits.p, closest.p, color.p, seeds.p, hist.p, counts.p, sums, npix};
+	}
+	WaveDev wave() {
+		WaveDev w{};
+		for (int k = 0; k < 2; ++k) { w.od[k] = od[k].p; w.dp[k] = dp[k].p; w.cs[k] = cs[k].p; }
+		w.sample_out = sample_out.p;
+		w.qcount = qcount.p;
+		w.first_sample = first_sample.p;
+		w.rays_traced = counters.p + 3;
+		w.paths_done = counters.p + 4;
+		w.seeds = seeds.p;
+		w.hist = hist.p;
+		w.counts = counts.p;
+		w.sums = sums;
+		w.npix = npix;
+		return w;
+	}
+	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
+};
+
+namespace {
+
+inline int blocks(long n, int bs) { return int((n + bs - 1) / bs); }
+
+int check_ctx(mcpt_ctx* c, bool need_scene, bool need_camera) {
+	if (!c) return fail(MCPT_ERR_ARG, "null context");
+	if (need_scene && !c->have_scene) return fail(MCPT_ERR_STATE, "scene not uploaded (mcpt_upload_scene)");
+	if (need_camera && !c->have_camera) return fail(MCPT_ERR_STATE, "camera not set (mcpt_set_camera)");
+	cudaError_t e = cudaSetDevice(c->prm.device);
+	if (e != cudaSuccess) return fail(MCPT_ERR_CUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+	return MCPT_OK;
+}
+
+int ensure_wave(mcpt_ctx* c, int samples) {
+	if (samples <= c->wave_samples) return MCPT_OK;
+	size_t n = size_t(samples) * size_t(c->npix);
+	for (int k = 0; k < 2; ++k) {
+		CU(c->od[k].alloc(n));
+		CU(c->dp[k].alloc(n));
+		CU(c->cs[k].alloc(n));
+	}
+	CU(c->sample_out.alloc(n));
+	c->wave_samples = samples;
+	return MCPT_OK;
+}
+
+int reset_accumulation(mcpt_ctx* c) {
+	const int n = c->npix;
+	CU(cudaMemsetAsync(c->hist.p, 0, sizeof(float4) * n, c->stream));
+	CU(cudaMemsetAsync(c->counts.p, 0, sizeof(int32_t) * n, c->stream));
+	CU(cudaMemsetAsync(c->sums, 0, sizeof(double) * 7 * size_t(n), c->stream));
+	CU(cudaMemsetAsync(c->first_sample.p, 0, sizeof(uint32_t), c->stream));
+	k_init_seeds<<<blocks(n, 256), 256, 0, c->stream>>>(c->seeds.p, n, c->prm.run_seed);
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+// One wave of the fused pipeline: nsamples consecutive samples of every pixel.
+int enqueue_wave(mcpt_ctx* c, int nsamples) {
+	const int D = c->prm.max_depth;
+	const long total = long(nsamples) * c->npix;
+	WaveDev w = c->wave();
+	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
+	const int trav = c->traversal(c->prm.traversal);
+	for (int d = 0; d < D; ++d) {
+		if (trav == MCPT_TRAVERSAL_REFERENCE)
+			k_wave_bounce<MCPT_TRAVERSAL_REFERENCE><<<blocks(total, 128), 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode);
+		else
+			k_wave_bounce<MCPT_TRAVERSAL_FAST><<<blocks(total, 128), 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode);
+	}
+	k_wave_resolve<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, nsamples, D, c->prm.max_attempt);
+	c->launches += uint64_t(D) + 2;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal, bool count) {
+	const int trav = c->traversal(traversal);
+	const int g = blocks(n, 128);
+	unsigned long long* cnt = c->counters.p;
+	if (trav == MCPT_TRAVERSAL_REFERENCE) {
+		if (count) k_intersect<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
+		else k_intersect<MCPT_TRAVERSAL_REFERENCE, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
+	} else if (trav == MCPT_TRAVERSAL_FAST) {
+		if (count) k_intersect<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
+		else k_intersect<MCPT_TRAVERSAL_FAST, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
+	} else {
+		return fail(MCPT_ERR_ARG, "unknown traversal");
+	}
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+}  // namespace
+
+// ================================================================== C ABI
+extern "C" {
+
+const char* mcpt_last_error(void) { return g_err.c_str(); }
+int mcpt_abi_version(void) { return 1; }
+
+mcpt_ctx* mcpt_create(const mcpt_params* params) {
+	if (!params || params->width <= 0 || params->height <= 0 || params->max_depth <= 0 || params->max_depth > 0xFFFF ||
+	    params->max_attempt < 0 || long(params->width) * params->height > (1L << 28)) {
+		fail(MCPT_ERR_ARG, "mcpt_create: bad parameters");
+		return nullptr;
+	}
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0) {
+		fail(MCPT_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e));
+		return nullptr;
+	}
+	if (params->device < 0 || params->device >= ndev) { fail(MCPT_ERR_ARG, "mcpt_create: device ordinal out of range"); return nullptr; }
+	cudaDeviceProp prop{};
+	if ((e = cudaGetDeviceProperties(&prop, params->device)) != cudaSuccess || (e = cudaSetDevice(params->device)) != cudaSuccess) {
+		fail(MCPT_ERR_CUDA, cudaGetErrorString(e));
+		return nullptr;
+	}
+	if (prop.major != 10) {
+		fail(MCPT_ERR_CUDA, "this library carries sm_100a code only; device is sm_" + std::to_string(prop.major * 10 + prop.minor));
+		return nullptr;
+	}
+	mcpt_ctx* c = new mcpt_ctx();
+	c->prm = *params;
+	if (c->prm.tmin == 0.0f) c->prm.tmin = 0.001f;
+	if (c->prm.seed_mode == 0) c->prm.samples_in_flight = 1;
+	c->npix = params->width * params->height;
+	const size_t n = size_t(c->npix);
+	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
+	ok = ok && c->rays.alloc(n) == cudaSuccess && c->hits.alloc(n) == cudaSuccess && c->closest.alloc(n) == cudaSuccess &&
+	     c->color.alloc(n) == cudaSuccess && c->hist.alloc(n) == cudaSuccess && c->display.alloc(n) == cudaSuccess &&
+	     c->seeds.alloc(n) == cudaSuccess && c->counts.alloc(n) == cudaSuccess && c->sums_own.alloc(7 * n) == cudaSuccess &&
+	     c->qcount.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->first_sample.alloc(1) == cudaSuccess &&
+	     c->counters.alloc(8) == cudaSuccess;
+	if (ok) {
+		c->sums = c->sums_own.p;
+		ok = cudaMemsetAsync(c->rays.p, 0, sizeof(mcpt_ray) * n, c->stream) == cudaSuccess &&
+		     cudaMemsetAsync(c->hits.p, 0, sizeof(mcpt_hit) * n, c->stream) == cudaSuccess &&
+		     cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * 8, c->stream) == cudaSuccess &&
+		     reset_accumulation(c) == MCPT_OK && cudaStreamSynchronize(c->stream) == cudaSuccess;
+	}
+	if (!ok) {
+		if (g_err.empty()) fail(MCPT_ERR_CUDA, std::string("mcpt_create: ") + cudaGetErrorString(cudaGetLastError()));
+		delete c;
+		return nullptr;
+	}
+	return c;
+}
+
+void mcpt_destroy(mcpt_ctx* c) {
+	if (!c) return;
+	cudaSetDevice(c->prm.device);
+	cudaStreamSynchronize(c->stream);
+	delete c;
+}
+
+void* mcpt_stream(mcpt_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+int mcpt_synchronize(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                      const mcpt_bvh_node* nodes, int nnodes) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
+		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
+	// ---- validate + derive the traversal layout (host side, once per scene)
+	std::vector<DTri> dt(ntris);
+	for (int i = 0; i < ntris; ++i) {
+		const mcpt_triangle& t = tris[i];
+		if (t.material_id < 0 || t.material_id >= nmats) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
+		DTri& d = dt[i];
+		d.v0x = t.v[0].x; d.v0y = t.v[0].y; d.v0z = t.v[0].z; d.material = t.material_id;
+		// e1 = -(v1 - v0), e2 = -(v2 - v0): the matrix rows of objdef.h:194-199
+		d.e1x = -(t.v[1].x - t.v[0].x); d.e1y = -(t.v[1].y - t.v[0].y); d.e1z = -(t.v[1].z - t.v[0].z);
+		d.e2x = -(t.v[2].x - t.v[0].x); d.e2y = -(t.v[2].y - t.v[0].y); d.e2z = -(t.v[2].z - t.v[0].z);
+		d.cr0 = d.e1y * d.e2z - d.e2y * d.e1z;
+		d.cr1 = d.e1x * d.e2z - d.e2x * d.e1z;
+		d.cr2 = d.e1x * d.e2y - d.e2x * d.e1y;
+		d.nx = t.nx; d.ny = t.ny; d.nz = t.nz;
+	}
+	for (int m = 0; m < nmats; ++m)
+		if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
+			return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
+	auto is_leaf = [&](int i) { return nodes[i].left == nodes[i].right; };
+	bool contained = true;
+	const bool root_leaf = is_leaf(0);
+	std::vector<DNode> dn(root_leaf ? 1 : size_t(nnodes));   // indexed by reference node id (leaf slots unused)
+	std::memset(dn.data(), 0, dn.size() * sizeof(DNode));
+	for (int i = 0; i < nnodes; ++i) {
+		const mcpt_bvh_node& nd = nodes[i];
+		if (nd.left < 0 || nd.right < 0) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: negative child index");
+		if (is_leaf(i)) {
+			if (nd.left >= ntris) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: leaf triangle index out of range");
+			continue;
+		}
+		if (nd.left >= nnodes || nd.right >= nnodes) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: child index out of range");
+		const mcpt_bvh_node& L = nodes[nd.left];
+		const mcpt_bvh_node& R = nodes[nd.right];
+		for (const mcpt_bvh_node* ch : {&L, &R}) {
+			if (!(ch->bbmin.x >= nd.bbmin.x && ch->bbmin.y >= nd.bbmin.y && ch->bbmin.z >= nd.bbmin.z &&
+			      ch->bbmax.x <= nd.bbmax.x && ch->bbmax.y <= nd.bbmax.y && ch->bbmax.z <= nd.bbmax.z))
+				contained = false;
+		}
+		if (root_leaf) continue;
+		DNode& d = dn[i];
+		d.lminx = L.bbmin.x; d.lminy = L.bbmin.y; d.lminz = L.bbmin.z; d.lmaxx = L.bbmax.x; d.lmaxy = L.bbmax.y; d.lmaxz = L.bbmax.z;
+		d.rminx = R.bbmin.x; d.rminy = R.bbmin.y; d.rminz = R.bbmin.z; d.rmaxx = R.bbmax.x; d.rmaxy = R.bbmax.y; d.rmaxz = R.bbmax.z;
+		d.left = is_leaf(nd.left) ? ~L.left : nd.left;
+		d.right = is_leaf(nd.right) ? ~R.left : nd.right;
+	}
+	// azimuth table of randomDirection (shade.cl:43): angle evaluated in double, narrowed, then cos/sin
+	std::vector<float2> cs(32768);
+	for (int r = 0; r < 32768; ++r) {
+		float deg = float(2 * 3.14159265358979323846 / 32768 * double(uint32_t(r)));
+		cs[r] = make_float2(float(std::cos(double(deg))), float(std::sin(double(deg))));
+	}
+	CU(cudaStreamSynchronize(c->stream));
+	CU(c->nodes_ref.alloc(nnodes));
+	CU(c->tris_ref.alloc(ntris));
+	CU(c->nodes.alloc(dn.size()));
+	CU(c->tris.alloc(ntris));
+	CU(c->mats.alloc(nmats));
+	CU(c->cs_table.alloc(32768));
+	CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->nodes.p, dn.data(), sizeof(DNode) * dn.size(), cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->tris.p, dt.data(), sizeof(DTri) * ntris, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->cs_table.p, cs.data(), sizeof(float2) * 32768, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	c->force_reference = !contained;
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->tris.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
+	c->have_scene = true;
+	return MCPT_OK;
+}
+
+int mcpt_set_camera(mcpt_ctx* c, const mcpt_camera* cam) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!cam) return fail(MCPT_ERR_ARG, "mcpt_set_camera: null camera");
+	CameraDev d{};
+	d.center = f4{cam->center.x, cam->center.y, cam->center.z, cam->center.w};
+	d.direction = f4{cam->direction.x, cam->direction.y, cam->direction.z, cam->direction.w};
+	d.up = f4{cam->up.x, cam->up.y, cam->up.z, cam->up.w};
+	d.horizontal = f4{cam->horizontal.x, cam->horizontal.y, cam->horizontal.z, cam->horizontal.w};
+	d.arg = cam->arg;
+	d.distance = 0.5f / float(std::tan(double(cam->arg / 2)));     // rayGenerator.cl:16, uniform over the image
+	d.camera_type = cam->camera_type;
+	d.width = uint32_t(c->prm.width);
+	d.height = uint32_t(c->prm.height);
+	c->cam = d;
+	c->have_camera = true;
+	return MCPT_OK;
+}
+
+// ---------------------------------------------------------------- stage level
+int mcpt_generate_rays(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, true)) return r;
+	dim3 bs(32, 8), gs((c->prm.width + 31) / 32, (c->prm.height + 7) / 8);
+	k_generate_rays<<<gs, bs, 0, c->stream>>>(c->cam, c->rays.p);
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int mcpt_reset_color(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, false)) return r;
+	k_fill_color<<<blocks(c->npix, 256), 256, 0, c->stream>>>(c->color.p, c->npix, 1.0f);
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int mcpt_intersect(mcpt_ctx* c, int traversal) {
+	if (int r = check_ctx(c, true, false)) return r;
+	// the live-ray counter (counters[2]) feeds stats.rays_traced for the stage path
+	const int trav = c->traversal(traversal);
+	const int g = blocks(c->npix, 128);
+	if (trav == MCPT_TRAVERSAL_REFERENCE)
+		k_intersect<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p);
+	else if (trav == MCPT_TRAVERSAL_FAST)
+		k_intersect<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p);
+	else
+		return fail(MCPT_ERR_ARG, "unknown traversal");
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int mcpt_shade(mcpt_ctx* c) {
+	if (int r = check_ctx(c, true, false)) return r;
+	k_shade<<<blocks(c->npix, 128), 128, 0, c->stream>>>(c->scene, c->rays.p, c->hits.p, c->color.p, c->seeds.p, c->npix, c->prm.max_depth);
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int mcpt_accumulate(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, false)) return r;
+	k_history<<<blocks(c->npix, 256), 256, 0, c->stream>>>(c->color.p, c->hist.p, c->counts.p, c->sums, c->npix, c->prm.max_attempt);
+	++c->launches;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+int mcpt_display(mcpt_ctx* c, int from_history, float* host_rgba) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!host_rgba) return fail(MCPT_ERR_ARG, "mcpt_display: null destination");
+	k_display<<<blocks(c->npix, 256), 256, 0, c->stream>>>(from_history ? c->hist.p : c->color.p, c->display.p, c->npix);
+	++c->launches;
+	CU(cudaGetLastError());
+	CU(cudaMemcpyAsync(host_rgba, c->display.p, sizeof(float4) * c->npix, cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_frame(mcpt_ctx* c) {
+	if (int r = check_ctx(c, true, true)) return r;
+	int r;
+	if ((r = mcpt_reset_color(c)) || (r = mcpt_generate_rays(c))) return r;
+	for (int d = 0; d < c->prm.max_depth; ++d)
+		if ((r = mcpt_intersect(c, c->prm.traversal)) || (r = mcpt_shade(c))) return r;
+	if ((r = mcpt_accumulate(c))) return r;
+	c->stage_paths += uint64_t(c->npix);
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+// ---------------------------------------------------------------- fused wavefront path
+int mcpt_render_async(mcpt_ctx* c, int spp) {
+	if (int r = check_ctx(c, true, true)) return r;
+	if (spp < 0) return fail(MCPT_ERR_ARG, "mcpt_render: negative spp");
+	int S = c->prm.seed_mode == 0 ? 1 : c->prm.samples_in_flight;
+	if (S <= 0) {   // automatic: about 4 Mi paths in flight
+		S = int((4L << 20) / c->npix);
+		if (S < 1) S = 1;
+		if (S > 64) S = 64;
+	}
+	if (S > spp && spp > 0) S = spp;
+	if (int r = ensure_wave(c, S)) return r;
+	for (int done = 0; done < spp;) {
+		int s = spp - done < S ? spp - done : S;
+		if (int r = enqueue_wave(c, s)) return r;
+		done += s;
+	}
+	return MCPT_OK;
+}
+
+int mcpt_render(mcpt_ctx* c, int spp) {
+	if (int r = mcpt_render_async(c, spp)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_set_first_sample(mcpt_ctx* c, uint32_t first) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaMemcpyAsync(c->first_sample.p, &first, sizeof(first), cudaMemcpyHostToDevice, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_reset_accumulation(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (int r = reset_accumulation(c)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+// ---------------------------------------------------------------- buffer I/O
+#define MCPT_IO(name, type, member, dir_read)                                                                     \
+	int name(mcpt_ctx* c, type* buf) {                                                                            \
+		if (int r = check_ctx(c, false, false)) return r;                                                         \
+		if (!buf) return fail(MCPT_ERR_ARG, #name ": null buffer");                                               \
+		if (dir_read) CU(cudaMemcpyAsync((void*)buf, c->member.p, sizeof(*c->member.p) * c->npix, cudaMemcpyDeviceToHost, c->stream)); \
+		else CU(cudaMemcpyAsync(c->member.p, (const void*)buf, sizeof(*c->member.p) * c->npix, cudaMemcpyHostToDevice, c->stream));    \
+		CU(cudaStreamSynchronize(c->stream));                                                                     \
+		return MCPT_OK;                                                                                           \
+	}
+MCPT_IO(mcpt_read_rays, mcpt_ray, rays, true)
+MCPT_IO(mcpt_write_rays, const mcpt_ray, rays, false)
+MCPT_IO(mcpt_write_hits, const mcpt_hit, hits, false)
+MCPT_IO(mcpt_read_color, float, color, true)
+MCPT_IO(mcpt_write_color, const float, color, false)
+MCPT_IO(mcpt_read_seeds, uint32_t, seeds, true)
+MCPT_IO(mcpt_write_seeds, const uint32_t, seeds, false)
+#undef MCPT_IO
+
+int mcpt_read_hits(mcpt_ctx* c, mcpt_hit* dst, int32_t* closest) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!dst) return fail(MCPT_ERR_ARG, "mcpt_read_hits: null buffer");
+	CU(cudaMemcpyAsync(dst, c->hits.p, sizeof(mcpt_hit) * c->npix, cudaMemcpyDeviceToHost, c->stream));
+	if (closest) CU(cudaMemcpyAsync(closest, c->closest.p, sizeof(int32_t) * c->npix, cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_read_history(mcpt_ctx* c, float* hist_rgba, int32_t* counts) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!hist_rgba) return fail(MCPT_ERR_ARG, "mcpt_read_history: null buffer");
+	CU(cudaMemcpyAsync(hist_rgba, c->hist.p, sizeof(float4) * c->npix, cudaMemcpyDeviceToHost, c->stream));
+	if (counts) CU(cudaMemcpyAsync(counts, c->counts.p, sizeof(int32_t) * c->npix, cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_read_sums(mcpt_ctx* c, double* dst) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!dst) return fail(MCPT_ERR_ARG, "mcpt_read_sums: null buffer");
+	CU(cudaMemcpyAsync(dst, c->sums, sizeof(double) * 7 * size_t(c->npix), cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_bind_sums(mcpt_ctx* c, double* device_ptr) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	c->sums = device_ptr ? device_ptr : c->sums_own.p;
+	return MCPT_OK;
+}
+
+// ---------------------------------------------------------------- microbench / ad-hoc queries
+int mcpt_trace_device(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal) {
+	if (int r = check_ctx(c, true, false)) return r;
+	if (!d_rays || !d_hits || n < 0) return fail(MCPT_ERR_ARG, "mcpt_trace_device: bad arguments");
+	if (n == 0) return MCPT_OK;
+	return launch_intersect(c, d_rays, n, d_hits, d_closest, traversal, false);
+}
+
+int mcpt_trace_count(mcpt_ctx* c, const mcpt_ray* d_rays, long n, int traversal) {
+	if (int r = check_ctx(c, true, false)) return r;
+	if (!d_rays || n <= 0) return fail(MCPT_ERR_ARG, "mcpt_trace_count: bad arguments");
+	if (c->t_hits.n < size_t(n)) CU(c->t_hits.alloc(n));
+	CU(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * 3, c->stream));
+	if (int r = launch_intersect(c, d_rays, n, c->t_hits.p, nullptr, traversal, true)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_trace(mcpt_ctx* c, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_t* closest, int traversal) {
+	if (int r = check_ctx(c, true, false)) return r;
+	if (n < 0 || (n > 0 && (!rays || !hits))) return fail(MCPT_ERR_ARG, "mcpt_trace: bad arguments");
+	if (n == 0) return MCPT_OK;
+	// chunked so that a 64 Mi-ray batch needs bounded scratch; copies and kernels are stream ordered
+	const long CH = 8L << 20;
+	const long cap = n < CH ? n : CH;
+	if (c->t_rays.n < size_t(cap)) { CU(c->t_rays.alloc(cap)); CU(c->t_hits.alloc(cap)); CU(c->t_closest.alloc(cap)); }
+	if (c->t_hits.n < size_t(cap)) CU(c->t_hits.alloc(cap));
+	for (long off = 0; off < n; off += CH) {
+		const long m = n - off < CH ? n - off : CH;
+		CU(cudaMemcpyAsync(c->t_rays.p, rays + off, sizeof(mcpt_ray) * m, cudaMemcpyHostToDevice, c->stream));
+		if (int r = launch_intersect(c, c->t_rays.p, m, c->t_hits.p, c->t_closest.p, traversal, false)) return r;
+		CU(cudaMemcpyAsync(hits + off, c->t_hits.p, sizeof(mcpt_hit) * m, cudaMemcpyDeviceToHost, c->stream));
+		if (closest) CU(cudaMemcpyAsync(closest + off, c->t_closest.p, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, c->stream));
+	}
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!out) return fail(MCPT_ERR_ARG, "mcpt_get_stats: null output");
+	unsigned long long h[8];
+	CU(cudaMemcpyAsync(h, c->counters.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	out->nodes_fetched = h[0];
+	out->tris_fetched = h[1];
+	out->rays_traced = h[2] + h[3];
+	out->paths = h[4] + c->stage_paths;
+	out->kernel_launches = c->launches;
+	return MCPT_OK;
+}
+
+int mcpt_reset_stats(mcpt_ctx* c) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * 8, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	c->launches = 0;
+	c->stage_paths = 0;
+	return MCPT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,303 @@
+// Device-side arithmetic of the path tracer: the reference kernels' math with the implementation-
+// defined parts of OpenCL C pinned down (no FMA contraction: the translation unit is compiled with
+// -fmad=false; IEEE round-to-nearest + - * / sqrt; dot() accumulates left to right; fmin/fmax ignore
+// NaN).  Every function cites the reference lines it computes.
+#pragma once
+
+#include <cfloat>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "mcpt_types.h"
+
+namespace mcpt {
+
+constexpr float KERNEL_EPSILON = 1e-5f;   // objdef.h:16
+constexpr float TWO_PI_F = 6.28318530717958647692f;   // (float)(2*M_PI), shade.cl:120
+
+struct f4 { float x, y, z, w; };
+__device__ __forceinline__ f4 operator+(f4 a, f4 b) { return {a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w}; }
+__device__ __forceinline__ f4 operator-(f4 a, f4 b) { return {a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w}; }
+__device__ __forceinline__ f4 operator*(f4 a, f4 b) { return {a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w}; }
+__device__ __forceinline__ f4 operator*(float s, f4 a) { return {s * a.x, s * a.y, s * a.z, s * a.w}; }
+__device__ __forceinline__ f4 operator*(f4 a, float s) { return {a.x * s, a.y * s, a.z * s, a.w * s}; }
+__device__ __forceinline__ f4 operator/(f4 a, float s) { return {a.x / s, a.y / s, a.z / s, a.w / s}; }
+__device__ __forceinline__ f4 operator-(f4 a) { return {-a.x, -a.y, -a.z, -a.w}; }
+__device__ __forceinline__ float dot3(f4 a, f4 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float dot4(f4 a, f4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+__device__ __forceinline__ f4 normalize4(f4 a) { return a / sqrtf(dot4(a, a)); }
+__device__ __forceinline__ f4 cross4(f4 a, f4 b) {
+	return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x, 0.0f};
+}
+__device__ __forceinline__ f4 ld4(const mcpt_float4& v) { return {v.x, v.y, v.z, v.w}; }
+__device__ __forceinline__ f4 ld4(float4 v) { return {v.x, v.y, v.z, v.w}; }
+__device__ __forceinline__ float4 st4(f4 v) { return make_float4(v.x, v.y, v.z, v.w); }
+
+// Transcendentals: the correctly rounded float result, obtained by evaluating in double and
+// narrowing (the oracle does the same with libm).
+__device__ __forceinline__ float cr_pow(float x, float y) { return float(pow(double(x), double(y))); }
+__device__ __forceinline__ float cr_pow5(float x) {     // pow(x, 5) for calcFresnel, shade.cl:72
+	double d = double(x), d2 = d * d;
+	return float(d2 * d2 * d);
+}
+__device__ __forceinline__ float cr_sqr(float x) { double d = double(x); return float(d * d); }   // pow(x, 2)
+
+// ------------------------------------------------------------------ camera / K1 (rayGenerator.cl:1-31)
+struct CameraDev {
+	f4 center, direction, up, horizontal;
+	float arg;
+	float distance;         // 0.5f / tan(arg / 2), uniform over the image: evaluated once on the host
+	uint32_t camera_type;
+	uint32_t width, height;
+};
+
+struct RayRegs {            // Ray as the kernels hold it: float4 origin/direction with the aliased w words
+	f4 origin, direction;
+};
+
+__device__ __forceinline__ RayRegs generate_ray(const CameraDev& cam, uint32_t idx, uint32_t idy) {
+	uint32_t id = idy * cam.width + idx;
+	float px = float(idx) / float(cam.width);
+	float py = float(idy) / float(cam.height);
+	float ratio = float(cam.width) * 1.0f / float(cam.height);
+	RayRegs r;
+	if (cam.camera_type == 0) {
+		float temp1 = px - 0.5f;
+		float temp2 = py - 0.5f;
+		f4 dd = cam.direction * cam.distance + temp1 * cam.horizontal * ratio + temp2 * cam.up;
+		r.origin = cam.center;
+		r.direction = normalize4(dd);
+	} else {
+		r.origin = cam.center + (px - 0.5f) * (cam.arg) * cam.horizontal * ratio + (py - 0.5f) * (cam.arg) * cam.up;
+		r.direction = normalize4(cam.direction);
+	}
+	r.origin.w = __int_as_float(0);
+	r.direction.w = __int_as_float(int(id));
+	return r;
+}
+
+// ------------------------------------------------------------------ box test (objdef.h:223-237)
+// Exact restatement: six IEEE divisions, NaN-ignoring fmin/fmax.  tnear is returned for pruning.
+__device__ __forceinline__ bool intersect_aabb_exact(float bminx, float bminy, float bminz, float bmaxx, float bmaxy,
+                                                     float bmaxz, const RayRegs& r, float tmin, float& tnear_out) {
+	float o1x = (bminx - r.origin.x) / r.direction.x, o1y = (bminy - r.origin.y) / r.direction.y,
+	      o1z = (bminz - r.origin.z) / r.direction.z;
+	float o2x = (bmaxx - r.origin.x) / r.direction.x, o2y = (bmaxy - r.origin.y) / r.direction.y,
+	      o2z = (bmaxz - r.origin.z) / r.direction.z;
+	float tnear = fmaxf(fmaxf(fminf(o1x, o2x), fminf(o1y, o2y)), fminf(o1z, o2z));
+	float tfar = fminf(fminf(fmaxf(o1x, o2x), fmaxf(o1y, o2y)), fmaxf(o1z, o2z));
+	tnear_out = tnear;
+	if (tfar < tnear || tfar < tmin) return false;
+	return true;
+}
+
+// ------------------------------------------------------------------ triangle test (objdef.h:178-221)
+// The reference solves [Rd | -AB | -AC] (t,b,c)^T = A - Ro through a generic 4x4 cofactor inverse whose
+// last row/column is (0,0,0,1); every cofactor collapses exactly (x0, x1, +0 are exact) to a 2x2
+// determinant of the 3x3 block, so the expressions below are the surviving operations in the same
+// order (the oracle checks literal == reduced bit for bit).  e1 = -AB, e2 = -AC; cr = the three
+// ray-independent 2x2 determinants (e1.y*e2.z - e2.y*e1.z, e1.x*e2.z - e2.x*e1.z, e1.x*e2.y - e2.x*e1.y),
+// precomputed on the host in the same float arithmetic.
+struct TriTest { float t; bool valid; };
+
+__device__ __forceinline__ TriTest intersect_triangle(const RayRegs& ray, float v0x, float v0y, float v0z, float e1x,
+                                                      float e1y, float e1z, float e2x, float e2y, float e2z, float cr0,
+                                                      float cr1, float cr2, float nx, float ny, float nz, float tmin) {
+	TriTest out{0.0f, false};
+	const float a1 = ray.direction.x, a2 = ray.direction.y, a3 = ray.direction.z;
+	if (fabsf(nx * a1 + ny * a2 + nz * a3) < KERNEL_EPSILON) return out;      // :186
+	const float T2 = a2 * e2z - e2y * a3;
+	const float T3 = a2 * e1z - e1y * a3;
+	const float det = a1 * cr0 - e1x * T2 + e2x * T3;                          // det4x4, :150
+	if (fabsf(det) < KERNEL_EPSILON) return out;                               // :152
+	const float Ax = v0x - ray.origin.x, Ay = v0y - ray.origin.y, Az = v0z - ray.origin.z;
+	// the comparisons of :209 are evaluated lazily; they are a pure OR, so the outcome is the same
+	const float s1 = -T2 / det, s5 = (a1 * e2z - e2x * a3) / det, s9 = -(a1 * e2y - e2x * a2) / det;
+	const float b = Ax * s1 + Ay * s5 + Az * s9;
+	if (b < 0) return out;
+	const float s2 = T3 / det, s6 = -(a1 * e1z - e1x * a3) / det, s10 = (a1 * e1y - e1x * a2) / det;
+	const float c = Ax * s2 + Ay * s6 + Az * s10;
+	if (c < 0 || b + c > 1) return out;
+	const float s0 = cr0 / det, s4 = -cr1 / det, s8 = cr2 / det;
+	const float t = Ax * s0 + Ay * s4 + Az * s8;
+	if (t <= tmin) return out;
+	out.t = t;
+	out.valid = true;
+	return out;
+}
+
+// ------------------------------------------------------------------ K3 helpers (shade.cl:1-73)
+__device__ __forceinline__ uint32_t lcg_random(uint32_t& x) {               // :1-6
+	x = x * 1103515245u + 12345u;
+	return (x >> 16) & 0x00007FFFu;
+}
+
+__device__ __forceinline__ f4 mirror_direction(f4 normal, f4 incoming) {    // :19-25
+	normal.w = 0;
+	incoming.w = 0;
+	f4 ans = incoming - 2 * dot4(normal, incoming) * normal;
+	ans.w = 0;
+	return normalize4(ans);
+}
+
+__device__ __forceinline__ bool transmitted_direction(f4 normal, f4 incoming, float index_i, float index_t, f4& out) {   // :27-38
+	normal.w = 0;
+	incoming.w = 0;
+	float ita_r = index_i / index_t;
+	float n_dot_i = -dot4(normal, incoming);
+	float temp = 1.0f - ita_r * ita_r * (1 - n_dot_i * n_dot_i);
+	if (temp < 0.0f) return false;
+	out = normalize4((ita_r * n_dot_i - sqrtf(temp)) * normal + ita_r * incoming);
+	return true;
+}
+
+// cos/sin of the 32768 possible azimuths 2*pi*r/32768 (shade.cl:43): tabulated on the host as the
+// correctly rounded float of cos/sin of the FLOAT angle, interleaved (cos, sin).
+__device__ __forceinline__ f4 random_direction(f4 normal, uint32_t& seed, const float2* __restrict__ cs_table) {   // :40-59
+	normal.w = 0;
+	uint32_t r1 = lcg_random(seed);
+	float deg2 = float(lcg_random(seed)) * 1.0f / 32768.0f;
+	float s = sqrtf(deg2);
+	f4 axis1 = (normal.z == 0) ? f4{0, 0, 1.0f, 0} : f4{1, 0, 0, 0};
+	f4 axis2 = normalize4(cross4(axis1, normal));
+	axis1 = normalize4(cross4(axis2, normal));
+	float2 cs = __ldg(cs_table + r1);
+	return normalize4(cs.x * s * axis1 + cs.y * s * axis2 + (1 - deg2) * normal);
+}
+
+__device__ __forceinline__ float calc_fresnel(f4 normal, f4 incoming, float ior) {   // :69-73
+	float k = cr_sqr((ior - 1) / (ior + 1));
+	return k + (1 - k) * cr_pow5(1 - fabsf(dot3(normal, incoming)));
+}
+
+// shade.cl:75-206 for one work item.  ray.origin.w carries the state word.  Returns true when the
+// path goes on (ray updated), false when it terminated (color final).  `color` has 4 lanes like the
+// reference's float4.
+struct MaterialDev {
+	int32_t type;
+	float Ni, Ns, pad;
+	f4 kd, ka_ks;
+};
+
+__device__ __forceinline__ MaterialDev load_material(const mcpt_material* __restrict__ mats, uint32_t id) {
+	const float4* p = reinterpret_cast<const float4*>(mats + id);
+	float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+	MaterialDev m;
+	m.type = __float_as_int(a.x);
+	m.Ni = a.y; m.Ns = a.z; m.pad = a.w;
+	m.kd = ld4(b);
+	m.ka_ks = ld4(c);
+	return m;
+}
+
+__device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
+                                          RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
+                                          uint32_t& seed_slot, int max_depth) {
+	const uint32_t state = uint32_t(__float_as_int(ray.origin.w));
+	if (hit_t >= FLT_MAX) {                                                   // :92-96
+		color = f4{0, 0, 0, 0};
+		ray.origin.w = __int_as_float(int(state | MCPT_RAY_TERM_MASK));
+		return false;
+	}
+	const f4 my_dir = ray.direction;
+	uint32_t seed = seed_slot;
+	const MaterialDev mat = load_material(mats, material_id);
+	f4 new_dir{0, 0, 0, 0}, new_org{0, 0, 0, 0};
+	int32_t new_state = 0;
+	switch (mat.type) {
+	case MCPT_DIFFUSE: {                                                      // :114-123
+		new_dir = random_direction(n, seed, cs_table);
+		new_org = ip + KERNEL_EPSILON * new_dir;
+		new_state = int32_t(state) + 1;
+		color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
+		seed_slot = seed;
+		break;
+	}
+	case MCPT_GLOSSY: {                                                       // :124-154
+		if (lcg_random(seed) & 1u) {
+			f4 reflect = mirror_direction(n, my_dir);
+			new_dir = random_direction(reflect, seed, cs_table);
+			while (dot3(new_dir, n) <= 0) new_dir = random_direction(reflect, seed, cs_table);
+			new_org = ip + KERNEL_EPSILON * new_dir;
+			new_state = int32_t(state) + 1;
+			color = color * mat.ka_ks * cr_pow(dot3(new_dir, reflect), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
+		} else {
+			new_dir = random_direction(n, seed, cs_table);
+			new_org = ip + KERNEL_EPSILON * new_dir;
+			new_state = int32_t(state) + 1;
+			color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
+		}
+		seed_slot = seed;
+		break;
+	}
+	case MCPT_LIGHT:                                                          // :155-158
+		ray.origin.w = __int_as_float(int(state | MCPT_RAY_TERM_MASK));
+		color = color * mat.ka_ks;
+		return false;
+	case MCPT_TRANSPARENT: {                                                  // :159-193
+		bool in_obj = (state & MCPT_RAY_INSIDE_MASK) != 0;
+		float i = in_obj ? mat.Ni : 1.0f;
+		float t = in_obj ? 1.0f : mat.Ni;
+		bool transmit = transmitted_direction(n, my_dir, i, t, new_dir);
+		new_org = ip;
+		new_state = int32_t(state) + 1;
+		if (!transmit) {
+			new_dir = mirror_direction(n, my_dir);
+		} else {
+			float fresnel = calc_fresnel(n, new_dir, mat.Ni);
+			if ((float(lcg_random(seed)) * 1.0f / 32768.0f) >= fresnel) {
+				new_state = int32_t(uint32_t(new_state) ^ MCPT_RAY_INSIDE_MASK);
+			} else {
+				f4 m = mirror_direction(n, my_dir);
+				new_dir.x = m.x; new_dir.y = m.y; new_dir.z = m.z;
+			}
+			seed_slot = seed;
+		}
+		break;
+	}
+	default:
+		break;   // the reference prints "Crash!!!" (shade.cl:195) and stores an uninitialised ray
+	}
+	bool alive = true;
+	if ((uint32_t(new_state) & MCPT_RAY_DEPTH_MASK) >= uint32_t(max_depth)) {   // :199-202
+		color = f4{0, 0, 0, 0};
+		new_state = int32_t(uint32_t(new_state) | MCPT_RAY_TERM_MASK);
+		alive = false;
+	}
+	const float pixel_w = ray.direction.w;
+	ray.origin = f4{new_org.x, new_org.y, new_org.z, __int_as_float(new_state)};
+	ray.direction = f4{new_dir.x, new_dir.y, new_dir.z, pixel_w};
+	return alive;
+}
+
+// ------------------------------------------------------------------ K4 (history.cl:3-28)
+__device__ __forceinline__ bool history_one(f4& new_color, f4& hist, int32_t& count, int max_attempt) {
+	f4 now = new_color;
+	if (sqrtf(dot4(now, now)) == 0 || count >= max_attempt) {
+		new_color = hist;
+		return false;
+	}
+	now = (now + hist * float(count)) / float(count + 1);
+	hist = now;
+	new_color = now;
+	hist.w = 0.0f;
+	++count;
+	return true;
+}
+
+// ------------------------------------------------------------------ deterministic seeding (replaces
+// srand(time(NULL)); rand() per pixel, scenebuild.cpp:116-119)
+__host__ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
+	x ^= x >> 16; x *= 0x7feb352du;
+	x ^= x >> 15; x *= 0x846ca68bu;
+	x ^= x >> 16;
+	return x;
+}
+__host__ __device__ __forceinline__ uint32_t pixel_seed(uint32_t pixel, uint32_t run_seed) {
+	return mix32(pixel ^ mix32(run_seed)) & 0x7FFFu;     // MSVC rand() range
+}
+__host__ __device__ __forceinline__ uint32_t sample_seed(uint32_t pixel, uint32_t sample, uint32_t run_seed) {
+	return mix32(pixel ^ mix32(sample ^ mix32(run_seed)));
+}
+
+}  // namespace mcpt

@@ -1,0 +1,267 @@
+// Kernels of the path-tracing hot path.
+//
+// Stage kernels (k_generate_rays, k_intersect, k_shade, k_history, k_display) are one-to-one with the
+// reference's five OpenCL kernels and work on the reference's buffer layouts (Ray 48 B, Hit 48 B,
+// colour float4, seed u32): they are the drop-in surface behind RayGeneration/SceneBase/ColorOut.
+//
+// Wavefront kernels (k_wave_generate, k_wave_bounce, k_wave_resolve) are the product path used by
+// mcpt_render: path state lives in three float4 streams that are compacted at every bounce
+// (warp ballot + prefix popcount + one atomic per warp), traversal and shading are fused so no Hit
+// record is ever materialised, and finished samples are folded into the accumulators in sample order,
+// which makes the running mean bit-identical to history.cl's frame-by-frame update.
+#pragma once
+
+#include "mcpt_traverse.cuh"
+
+namespace mcpt {
+
+struct FrameDev {               // reference-layout per-pixel buffers (stage path)
+	mcpt_ray* rays;
+	mcpt_hit* hits;
+	int32_t* closest;
+	float4* color;
+	uint32_t* seeds;
+	float4* hist;
+	int32_t* counts;
+	double* sums;               // 7 planes of n doubles
+	int n;
+};
+
+__device__ __forceinline__ RayRegs load_ray(const mcpt_ray* rays, long i) {
+	const float4* p = reinterpret_cast<const float4*>(rays + i);
+	float4 o = p[0], d = p[1];
+	return {ld4(o), ld4(d)};
+}
+__device__ __forceinline__ void store_ray(mcpt_ray* rays, long i, const RayRegs& r) {
+	float4* p = reinterpret_cast<float4*>(rays + i);
+	p[0] = st4(r.origin);
+	p[1] = st4(r.direction);
+	// Ray.ratio is never written by the reference kernels
+}
+
+// ------------------------------------------------------------------ K1
+__global__ void k_generate_rays(CameraDev cam, mcpt_ray* rays) {
+	uint32_t x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y * blockDim.y + threadIdx.y;
+	if (x >= cam.width || y >= cam.height) return;
+	RayRegs r = generate_ray(cam, x, y);
+	store_ray(rays, long(y) * cam.width + x, r);
+}
+
+__global__ void k_fill_color(float4* color, int n, float v) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) color[i] = make_float4(v, v, v, v);
+}
+
+// ------------------------------------------------------------------ K2  (intersect.cl:1-28)
+// Writes the 48-byte Hit of the reference; `closest` (optional) gets the triangle whose data is in it.
+template <int TRAVERSAL, bool COUNT>
+__global__ void __launch_bounds__(128) k_intersect(SceneDev sc, const mcpt_ray* __restrict__ rays, long n, float tmin,
+                                                    mcpt_hit* __restrict__ hits, int32_t* __restrict__ closest,
+                                                    unsigned long long* counters) {
+	long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
+	bool live = false;
+	if (i < n) {
+		RayRegs ray = load_ray(rays, i);
+		uint32_t state = uint32_t(__float_as_int(ray.origin.w));
+		if (!(state & MCPT_RAY_TERM_MASK)) {
+			live = true;
+			HitRegs h{FLT_MAX, -1, 0, false};
+			if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+			else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+			float4 nrm = make_float4(0, 0, 0, 0), pt = make_float4(0, 0, 0, 0);
+			uint32_t mat = 0;
+			if (h.closest >= 0) {
+				const float4* tp = reinterpret_cast<const float4*>(sc.tris + h.closest);
+				float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3);
+				f4 nn{q1.w, q2.w, q3.w, 0.0f};
+				mat = uint32_t(__float_as_int(q0.w));
+				pt = st4(ray.origin + h.t * ray.direction);            // 4 lanes, like the float4 expression at objdef.h:218
+				if (h.any && dot3(ray.direction, nn) > 0) nn = -nn;    // intersect.cl:23-25
+				nrm = st4(nn);
+			}
+			float4* hp = reinterpret_cast<float4*>(hits + i);
+			hp[0] = nrm;
+			hp[1] = pt;
+			uint32_t tid = TRAVERSAL == MCPT_TRAVERSAL_REFERENCE ? uint32_t(h.last_touched)
+			                                                     : uint32_t(h.closest >= 0 ? h.closest : 0);
+			hp[2] = make_float4(h.t, __int_as_float(int(tid)), __int_as_float(int(mat)), __int_as_float(0));
+			if (closest) closest[i] = h.closest;
+		} else if (closest) {
+			closest[i] = -1;
+		}
+	}
+	if (COUNT) {      // live-ray counter in counters[2]
+		unsigned m = __ballot_sync(0xffffffffu, live);
+		if ((threadIdx.x & 31) == 0 && m) atomicAdd(counters + 2, (unsigned long long)__popc(m));
+	}
+}
+
+// ------------------------------------------------------------------ K3  (shade.cl:75-206)
+__global__ void __launch_bounds__(128) k_shade(SceneDev sc, mcpt_ray* rays, const mcpt_hit* __restrict__ hits,
+                                                float4* color, uint32_t* seeds, int n, int max_depth) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	RayRegs ray = load_ray(rays, i);
+	if (uint32_t(__float_as_int(ray.origin.w)) & MCPT_RAY_TERM_MASK) return;     // :89
+	const float4* hp = reinterpret_cast<const float4*>(hits + i);
+	float4 nrm = hp[0], pt = hp[1], misc = hp[2];
+	f4 c = ld4(color[i]);
+	uint32_t seed = seeds[i];
+	shade_one(sc.materials, sc.cs_table, ray, misc.x, ld4(nrm), ld4(pt), uint32_t(__float_as_int(misc.z)), c, seed, max_depth);
+	color[i] = st4(c);
+	seeds[i] = seed;
+	store_ray(rays, i, ray);
+}
+
+// ------------------------------------------------------------------ K4  (history.cl:3-28) + sums
+__global__ void k_history(float4* color, float4* hist, int32_t* counts, double* sums, int n, int max_attempt) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	f4 c = ld4(color[i]), h = ld4(hist[i]);
+	int32_t cnt = counts[i];
+	f4 raw = c;
+	if (history_one(c, h, cnt, max_attempt)) {
+		sums[i] += raw.x; sums[size_t(n) + i] += raw.y; sums[2 * size_t(n) + i] += raw.z;
+		sums[3 * size_t(n) + i] += double(raw.x) * raw.x;
+		sums[4 * size_t(n) + i] += double(raw.y) * raw.y;
+		sums[5 * size_t(n) + i] += double(raw.z) * raw.z;
+		sums[6 * size_t(n) + i] += 1.0;
+	}
+	color[i] = st4(c);
+	hist[i] = st4(h);
+	counts[i] = cnt;
+}
+
+// ------------------------------------------------------------------ K5  (testkernel.cl:9-14)
+__global__ void k_display(const float4* __restrict__ src, float4* dst, int n) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	float4 c = src[i];
+	const float g = 1 / 2.2f;
+	dst[i] = make_float4(cr_pow(c.x, g), cr_pow(c.y, g), cr_pow(c.z, g), 0.0f);
+}
+
+// ================================================================== wavefront path
+struct WaveDev {
+	float4* od[2];          // origin.xyz + state word          (double buffered)
+	float4* dp[2];          // direction.xyz + path id
+	float4* cs[2];          // throughput rgb + LCG state
+	float4* sample_out;     // finished samples, [s * npix + pixel] = (r, g, b, 0)
+	uint32_t* qcount;       // qcount[d] = live paths entering bounce d
+	uint32_t* first_sample; // device-resident global sample index of the wave's first sample
+	unsigned long long* rays_traced;
+	unsigned long long* paths_done;
+	uint32_t* seeds;        // per-pixel persistent LCG state (seed_mode 0)
+	float4* hist;
+	int32_t* counts;
+	double* sums;
+	int npix;
+};
+
+__global__ void __launch_bounds__(256) k_wave_generate(CameraDev cam, WaveDev w, int nsamples, int seed_mode, uint32_t run_seed) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	int total = nsamples * w.npix;
+	if (i == 0) w.qcount[0] = uint32_t(total);
+	if (i >= total) return;
+	int s = i / w.npix, p = i - s * w.npix;
+	RayRegs r = generate_ray(cam, uint32_t(p) % cam.width, uint32_t(p) / cam.width);
+	uint32_t seed = seed_mode == 0 ? w.seeds[p] : sample_seed(uint32_t(p), *w.first_sample + uint32_t(s), run_seed);
+	w.od[0][i] = st4(r.origin);
+	w.dp[0][i] = make_float4(r.direction.x, r.direction.y, r.direction.z, __int_as_float(i));
+	w.cs[0][i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(int(seed)));
+}
+
+// One bounce for every live path: closest hit + shade + (terminate | compact into the next queue).
+template <int TRAVERSAL>
+__global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode) {
+	const int src = depth & 1, dst = src ^ 1;
+	const uint32_t total = w.qcount[depth];
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (blockIdx.x * blockDim.x >= total) return;          // whole block idle (uniform exit)
+	bool alive = false;
+	RayRegs ray;
+	f4 color;
+	uint32_t seed = 0;
+	int path = 0;
+	if (i < total) {
+		float4 o = w.od[src][i], d = w.dp[src][i], c = w.cs[src][i];
+		path = __float_as_int(d.w);
+		const int pixel = path % w.npix;
+		ray.origin = ld4(o);
+		ray.direction = f4{d.x, d.y, d.z, __int_as_float(pixel)};
+		color = f4{c.x, c.y, c.z, 0.0f};
+		seed = uint32_t(__float_as_int(c.w));
+		HitRegs h{FLT_MAX, -1, 0, false};
+		if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<false>(sc, ray, tmin, h, nullptr, nullptr);
+		else trace_fast<false>(sc, ray, tmin, h, nullptr, nullptr);
+		f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
+		uint32_t mat = 0;
+		if (h.closest >= 0) {
+			const float4* tp = reinterpret_cast<const float4*>(sc.tris + h.closest);
+			float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3);
+			nn = f4{q1.w, q2.w, q3.w, 0.0f};
+			mat = uint32_t(__float_as_int(q0.w));
+			ip = ray.origin + h.t * ray.direction;
+			if (dot3(ray.direction, nn) > 0) nn = -nn;
+		}
+		alive = shade_one(sc.materials, sc.cs_table, ray, h.t, nn, ip, mat, color, seed, max_depth);
+		if (!alive) {
+			w.sample_out[path] = make_float4(color.x, color.y, color.z, 0.0f);
+			if (seed_mode == 0) w.seeds[pixel] = seed;
+		}
+	}
+	// queue compaction: ballot + prefix popcount, one atomic per warp
+	const unsigned mask = __ballot_sync(0xffffffffu, alive);
+	if (mask) {
+		const int lane = threadIdx.x & 31;
+		uint32_t base = 0;
+		if (lane == 0) base = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(mask)));
+		base = __shfl_sync(0xffffffffu, base, 0);
+		if (alive) {
+			const uint32_t pos = base + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+			w.od[dst][pos] = st4(ray.origin);
+			w.dp[dst][pos] = make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path));
+			w.cs[dst][pos] = make_float4(color.x, color.y, color.z, __int_as_float(int(seed)));
+		}
+	}
+}
+
+// Fold the wave's finished samples into the accumulators, in sample order (history.cl semantics).
+__global__ void __launch_bounds__(256) k_wave_resolve(WaveDev w, int nsamples, int max_depth, int max_attempt) {
+	int p = blockIdx.x * blockDim.x + threadIdx.x;
+	if (p == 0) {
+		unsigned long long traced = 0;
+		for (int d = 0; d < max_depth; ++d) traced += w.qcount[d];
+		*w.rays_traced += traced;
+		*w.paths_done += (unsigned long long)nsamples * (unsigned long long)w.npix;
+		*w.first_sample += uint32_t(nsamples);
+	}
+	if (p >= w.npix) return;
+	f4 h = ld4(w.hist[p]);
+	int32_t cnt = w.counts[p];
+	double s0 = 0, s1 = 0, s2 = 0, q0 = 0, q1 = 0, q2 = 0, k = 0;
+	for (int s = 0; s < nsamples; ++s) {
+		f4 c = ld4(w.sample_out[size_t(s) * w.npix + p]);
+		f4 raw = c;
+		if (history_one(c, h, cnt, max_attempt)) {
+			s0 += raw.x; s1 += raw.y; s2 += raw.z;
+			q0 += double(raw.x) * raw.x; q1 += double(raw.y) * raw.y; q2 += double(raw.z) * raw.z;
+			k += 1.0;
+		}
+	}
+	w.hist[p] = st4(h);
+	w.counts[p] = cnt;
+	if (k > 0) {
+		const size_t n = size_t(w.npix);
+		w.sums[p] += s0; w.sums[n + p] += s1; w.sums[2 * n + p] += s2;
+		w.sums[3 * n + p] += q0; w.sums[4 * n + p] += q1; w.sums[5 * n + p] += q2;
+		w.sums[6 * n + p] += k;
+	}
+}
+
+__global__ void k_init_seeds(uint32_t* seeds, int n, uint32_t run_seed) {
+	int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) seeds[i] = pixel_seed(uint32_t(i), run_seed);
+}
+
+}  // namespace mcpt

@@ -1,0 +1,253 @@
+"""ctypes binding of libmcpt_cuda.so (include/mcpt.h) — the CUDA hot path.
+
+The classes mirror the reference's stage interface so that tests read like the reference's call
+sites: RayGeneration.generateRay (raygeneration.cpp:29-35), SceneBase.intersect / .shade
+(scenebuild.cpp:103-145), ColorOut.outputColor (colorout.cpp:40-73) and OpenCLApp.update
+(OpenCLApp.cpp:57-82).  There is no CPU fallback: loading fails loudly when the library is missing
+and every call raises when no sm_100 device is usable.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+from . import types as T
+
+_PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+TRAVERSAL_REFERENCE, TRAVERSAL_FAST = 0, 1
+
+EXPORTS = [
+    "mcpt_last_error", "mcpt_abi_version", "mcpt_create", "mcpt_destroy", "mcpt_stream", "mcpt_synchronize",
+    "mcpt_upload_scene", "mcpt_set_camera", "mcpt_generate_rays", "mcpt_reset_color", "mcpt_intersect", "mcpt_shade",
+    "mcpt_accumulate", "mcpt_display", "mcpt_frame", "mcpt_render", "mcpt_render_async", "mcpt_set_first_sample",
+    "mcpt_reset_accumulation", "mcpt_read_rays", "mcpt_write_rays", "mcpt_read_hits", "mcpt_write_hits",
+    "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
+    "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
+    "mcpt_reset_stats",
+]
+
+
+class Params(ctypes.Structure):
+    _fields_ = [("width", ctypes.c_int), ("height", ctypes.c_int), ("max_depth", ctypes.c_int),
+                ("max_attempt", ctypes.c_int), ("device", ctypes.c_int), ("seed_mode", ctypes.c_int),
+                ("run_seed", ctypes.c_uint32), ("samples_in_flight", ctypes.c_int), ("tmin", ctypes.c_float),
+                ("traversal", ctypes.c_int), ("reserved", ctypes.c_int * 6)]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("rays_traced", ctypes.c_uint64), ("paths", ctypes.c_uint64), ("kernel_launches", ctypes.c_uint64),
+                ("nodes_fetched", ctypes.c_uint64), ("tris_fetched", ctypes.c_uint64)]
+
+
+def library_path():
+    return os.path.join(_PKG_DIR, "libmcpt_cuda.so")
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise RuntimeError("libmcpt_cuda.so is not built - run `python __graft_entry__.py` (there is no CPU fallback)")
+        L = ctypes.CDLL(path)
+        L.mcpt_last_error.restype = ctypes.c_char_p
+        L.mcpt_create.restype = ctypes.c_void_p
+        L.mcpt_create.argtypes = [ctypes.POINTER(Params)]
+        L.mcpt_stream.restype = ctypes.c_void_p
+        L.mcpt_stream.argtypes = [ctypes.c_void_p]
+        L.mcpt_destroy.restype = None
+        L.mcpt_destroy.argtypes = [ctypes.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def _vp(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(ctypes.c_void_p)
+    return ctypes.c_void_p(int(a))       # raw device pointer (e.g. torch.Tensor.data_ptr())
+
+
+class McptError(RuntimeError):
+    pass
+
+
+class Context:
+    """One device context = the reference's OpenCLApp state (OpenCLApp.cpp:17-33) for one scene."""
+
+    def __init__(self, width, height, max_depth, max_attempt, device=0, seed_mode=0, run_seed=1, samples_in_flight=0,
+                 tmin=0.001, traversal=TRAVERSAL_FAST):
+        self.width, self.height, self.max_depth, self.max_attempt = width, height, max_depth, max_attempt
+        self.npix = width * height
+        p = Params(width, height, max_depth, max_attempt, device, seed_mode, run_seed, samples_in_flight, tmin, traversal)
+        self._L = lib()
+        self._h = self._L.mcpt_create(ctypes.byref(p))
+        if not self._h:
+            raise McptError("mcpt_create: " + self._L.mcpt_last_error().decode())
+        self._h = ctypes.c_void_p(self._h)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.mcpt_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _call(self, name, *args):
+        rc = getattr(self._L, name)(self._h, *args)
+        if rc != 0:
+            raise McptError("%s: %s" % (name, self._L.mcpt_last_error().decode()))
+
+    @property
+    def stream(self):
+        return self._L.mcpt_stream(self._h)
+
+    def synchronize(self):
+        self._call("mcpt_synchronize")
+
+    # ---- OpenCL::init() pieces
+    def upload_scene(self, triangles, materials, nodes):
+        tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
+        mt = np.ascontiguousarray(materials, dtype=T.MATERIAL)
+        nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+        self._call("mcpt_upload_scene", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd))
+
+    def set_camera(self, camera):
+        cam = np.ascontiguousarray(camera, dtype=T.CAMERA)
+        self._call("mcpt_set_camera", _vp(cam))
+
+    # ---- stage level (RayGeneration / SceneBase / ColorOut)
+    def generate_rays(self):
+        self._call("mcpt_generate_rays")
+
+    def reset_color(self):
+        self._call("mcpt_reset_color")
+
+    def intersect(self, traversal=TRAVERSAL_FAST):
+        self._call("mcpt_intersect", traversal)
+
+    def shade(self):
+        self._call("mcpt_shade")
+
+    def accumulate(self):
+        self._call("mcpt_accumulate")
+
+    def display(self, from_history=True):
+        out = np.zeros((self.height, self.width, 4), np.float32)
+        self._call("mcpt_display", int(from_history), _vp(out))
+        return out
+
+    def frame(self):
+        self._call("mcpt_frame")
+
+    # ---- fused wavefront path
+    def render(self, spp):
+        self._call("mcpt_render", int(spp))
+
+    def render_async(self, spp):
+        self._call("mcpt_render_async", int(spp))
+
+    def set_first_sample(self, first):
+        self._call("mcpt_set_first_sample", ctypes.c_uint32(first))
+
+    def reset_accumulation(self):
+        self._call("mcpt_reset_accumulation")
+
+    # ---- buffer I/O
+    def read_rays(self):
+        out = np.zeros(self.npix, T.RAY)
+        self._call("mcpt_read_rays", _vp(out))
+        return out
+
+    def write_rays(self, rays):
+        r = np.ascontiguousarray(rays, dtype=T.RAY)
+        assert len(r) == self.npix
+        self._call("mcpt_write_rays", _vp(r))
+
+    def read_hits(self):
+        hits = np.zeros(self.npix, T.HIT)
+        closest = np.zeros(self.npix, np.int32)
+        self._call("mcpt_read_hits", _vp(hits), _vp(closest))
+        return hits, closest
+
+    def write_hits(self, hits):
+        h = np.ascontiguousarray(hits, dtype=T.HIT)
+        assert len(h) == self.npix
+        self._call("mcpt_write_hits", _vp(h))
+
+    def read_color(self):
+        out = np.zeros((self.npix, 4), np.float32)
+        self._call("mcpt_read_color", _vp(out))
+        return out
+
+    def write_color(self, color):
+        c = np.ascontiguousarray(color, dtype=np.float32).reshape(self.npix, 4)
+        self._call("mcpt_write_color", _vp(c))
+
+    def read_seeds(self):
+        out = np.zeros(self.npix, np.uint32)
+        self._call("mcpt_read_seeds", _vp(out))
+        return out
+
+    def write_seeds(self, seeds):
+        s = np.ascontiguousarray(seeds, dtype=np.uint32)
+        assert len(s) == self.npix
+        self._call("mcpt_write_seeds", _vp(s))
+
+    def read_history(self):
+        hist = np.zeros((self.npix, 4), np.float32)
+        counts = np.zeros(self.npix, np.int32)
+        self._call("mcpt_read_history", _vp(hist), _vp(counts))
+        return hist, counts
+
+    def read_sums(self):
+        out = np.zeros((7, self.npix), np.float64)
+        self._call("mcpt_read_sums", _vp(out))
+        return out
+
+    def bind_sums(self, device_ptr):
+        self._call("mcpt_bind_sums", _vp(device_ptr))
+
+    # ---- microbench
+    def trace(self, rays, traversal=TRAVERSAL_FAST, hits=None, closest=None):
+        r = rays if (isinstance(rays, np.ndarray) and rays.dtype == T.RAY and rays.flags.c_contiguous) \
+            else np.ascontiguousarray(rays, dtype=T.RAY)
+        n = len(r)
+        if hits is None:
+            hits = np.zeros(n, T.HIT)
+        if closest is None:
+            closest = np.zeros(n, np.int32)
+        self._call("mcpt_trace", _vp(r), ctypes.c_long(n), _vp(hits), _vp(closest), traversal)
+        return hits, closest
+
+    def trace_device(self, d_rays, n, d_hits, d_closest=None, traversal=TRAVERSAL_FAST):
+        self._call("mcpt_trace_device", _vp(d_rays), ctypes.c_long(n), _vp(d_hits), _vp(d_closest), traversal)
+
+    def trace_count(self, d_rays, n, traversal=TRAVERSAL_FAST):
+        self._call("mcpt_trace_count", _vp(d_rays), ctypes.c_long(n), traversal)
+        return self.stats()
+
+    def stats(self):
+        s = Stats()
+        self._call("mcpt_get_stats", ctypes.byref(s))
+        return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def reset_stats(self):
+        self._call("mcpt_reset_stats")
+
+
+def image_from_sums(sums, width, height):
+    """Mean of the counted (non-zero) samples = the reference's image (history.cl), from mergeable sums."""
+    n = np.maximum(sums[6], 1.0)
+    img = np.zeros((height, width, 4), np.float32)
+    img[..., :3] = (sums[:3] / n).T.reshape(height, width, 3)
+    return img
