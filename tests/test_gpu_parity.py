@@ -1,0 +1,176 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle on the
+same seeded inputs.  Bit-exact for rays, hit records, seeds and the accumulated image."""
+import numpy as np
+import pytest
+
+from montecarlopathtracing_b200 import device, types as T
+from oracle import oracle_api as O
+from tests.util import hit_mismatches, hits_equal, random_rays
+
+pytestmark = pytest.mark.gpu
+
+SCENE_RES = {"cbox": (256, 256), "mis": (320, 180)}
+
+
+def _ctx(sc, w, h, **kw):
+    kw.setdefault("max_depth", 8)
+    kw.setdefault("max_attempt", 16)
+    ctx = device.Context(w, h, **kw)
+    ctx.upload_scene(sc.triangles, sc.materials, sc.nodes)
+    ctx.set_camera(sc.camera)
+    return ctx
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_generate_rays_bit_exact(name, request):
+    sc = request.getfixturevalue(name)
+    w, h = SCENE_RES[name]
+    with _ctx(sc, w, h) as ctx:
+        ctx.generate_rays()
+        assert ctx.read_rays().tobytes() == O.generate_rays(sc.camera, w, h).tobytes()
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+@pytest.mark.parametrize("trav", [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST])
+def test_primary_hits_bit_exact(name, trav, request):
+    sc = request.getfixturevalue(name)
+    w, h = SCENE_RES[name]
+    rays = O.generate_rays(sc.camera, w, h)
+    ref_hits, ref_closest = O.intersect(rays, sc.nodes, sc.triangles)
+    with _ctx(sc, w, h) as ctx:
+        ctx.generate_rays()
+        ctx.intersect(trav)
+        hits, closest = ctx.read_hits()
+    assert np.array_equal(closest, ref_closest)
+    assert hits_equal(hits, ref_hits)
+    if trav == device.TRAVERSAL_REFERENCE:      # F7: raw "last triangle touched" field only from the reference walk
+        assert np.array_equal(hits["triangle_id"], ref_hits["triangle_id"])
+    if name == "cbox":                          # the lamp must win its coplanar ties
+        light = np.flatnonzero(sc.materials["type"] == T.LIGHT)
+        assert np.isin(hits["material_id"][closest >= 0], light).sum() > 0
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+@pytest.mark.parametrize("trav", [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST])
+def test_random_rays_bit_exact(name, trav, request):
+    sc = request.getfixturevalue(name)
+    rays = random_rays(200_000, sc.nodes)
+    ref_hits, ref_closest = O.intersect(rays, sc.nodes, sc.triangles)
+    with _ctx(sc, 64, 64) as ctx:
+        hits, closest = ctx.trace(rays, trav)
+    assert np.array_equal(closest, ref_closest)
+    assert hit_mismatches(hits, ref_hits) == 0
+
+
+def test_trace_edge_cases(cbox):
+    with _ctx(cbox, 64, 64) as ctx:
+        hits, closest = ctx.trace(np.zeros(0, T.RAY))           # empty batch
+        assert len(hits) == 0
+        rays = random_rays(1000, cbox.nodes, seed=3)
+        rays["direction"][::7, 0] = 0.0                          # zero components: Inf/NaN slab arithmetic
+        rays["direction"][::11, 1] = 0.0
+        rays["direction"][::13] = (0.0, 0.0, 1.0)
+        rays["state"][::5] = np.int32(-16777216)                 # terminated rays: hit record left untouched
+        ref_hits, ref_closest = O.intersect(rays, cbox.nodes, cbox.triangles)
+        for trav in (device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST):
+            hits, closest = ctx.trace(rays, trav)
+            live = (rays["state"].view(np.uint32) & T.RAY_TERM_MASK) == 0
+            assert np.array_equal(closest, ref_closest)
+            assert hit_mismatches(hits[live], ref_hits[live]) == 0
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_stage_loop_bit_exact(name, request):
+    """OpenCL::update() with the stage kernels: every intermediate buffer equals the oracle's."""
+    sc = request.getfixturevalue(name)
+    w, h = (96, 96) if name == "cbox" else (128, 72)
+    n = w * h
+    depth = 6
+    with _ctx(sc, w, h, max_depth=depth, run_seed=5) as ctx:
+        seeds = O.init_seeds(n, 5)
+        assert np.array_equal(ctx.read_seeds(), seeds)
+        hist = np.zeros((n, 4), np.float32)
+        counts = np.zeros(n, np.int32)
+        for frame in range(3):
+            rays = O.generate_rays(sc.camera, w, h)
+            color = np.ones((n, 4), np.float32)
+            hits = np.zeros(n, T.HIT)
+            ctx.reset_color()
+            ctx.generate_rays()
+            for d in range(depth):
+                O.intersect(rays, sc.nodes, sc.triangles, hits=hits)
+                O.shade(sc.materials, rays, hits, color, seeds, depth)
+                ctx.intersect(device.TRAVERSAL_FAST)
+                ctx.shade()
+                g_rays = ctx.read_rays()
+                for f in ("origin", "state", "direction", "pixel"):
+                    assert g_rays[f].tobytes() == rays[f].tobytes(), (frame, d, f)
+                assert ctx.read_color().tobytes() == color.tobytes(), (frame, d)
+                assert np.array_equal(ctx.read_seeds(), seeds), (frame, d)
+            O.history(color, hist, counts, 16)
+            ctx.accumulate()
+            g_hist, g_counts = ctx.read_history()
+            assert g_hist.tobytes() == hist.tobytes() and np.array_equal(g_counts, counts)
+            assert ctx.read_color().tobytes() == color.tobytes()
+        disp = ctx.display(from_history=True).reshape(n, 4)
+        ref_disp = O.display(hist)
+        assert np.max(np.abs(disp - ref_disp)) <= 1e-6
+
+
+@pytest.mark.parametrize("name,seed_mode,sif", [("cbox", 0, 0), ("cbox", 1, 4), ("mis", 0, 0), ("mis", 1, 3)])
+def test_render_bit_exact(name, seed_mode, sif, request):
+    """Fused wavefront render == oracle render of the same seeds (running mean, counts, ray count)."""
+    sc = request.getfixturevalue(name)
+    w, h = (128, 128) if name == "cbox" else (160, 90)
+    spp, depth, cap = 7, 8, 5
+    ref = O.render(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, depth, cap, spp, seed_mode=seed_mode, run_seed=11)
+    with _ctx(sc, w, h, max_depth=depth, max_attempt=cap, seed_mode=seed_mode, run_seed=11, samples_in_flight=sif) as ctx:
+        ctx.render(spp)
+        hist, counts = ctx.read_history()
+        sums = ctx.read_sums()
+        st = ctx.stats()
+    assert np.array_equal(counts, ref["counts"])
+    assert hist.tobytes() == ref["hist"].tobytes()
+    assert st["rays_traced"] == ref["rays_traced"]
+    assert st["paths"] == w * h * spp
+    np.testing.assert_allclose(sums[:3].T, ref["sum"], rtol=1e-12, atol=0)
+    np.testing.assert_allclose(sums[3:6].T, ref["sumsq"], rtol=1e-12, atol=0)
+    assert np.array_equal(sums[6], ref["counts"].astype(np.float64))
+
+
+def test_frame_equals_render(cbox):
+    """The stage-kernel frame loop and the fused wavefront give the same image for the same seeds."""
+    w = h = 64
+    with _ctx(cbox, w, h, run_seed=3) as a, _ctx(cbox, w, h, run_seed=3) as b:
+        for _ in range(4):
+            a.frame()
+        b.render(4)
+        ha, ca = a.read_history()
+        hb, cb = b.read_history()
+        assert ha.tobytes() == hb.tobytes() and np.array_equal(ca, cb)
+        assert a.stats()["rays_traced"] == b.stats()["rays_traced"]
+
+
+def test_sample_sharding_merges_exactly(cbox):
+    """Two contexts rendering disjoint sample ranges (seed_mode 1) merge to the single-context sums."""
+    w = h = 64
+    kw = dict(max_depth=8, max_attempt=1 << 20, seed_mode=1, run_seed=9, samples_in_flight=2)
+    with _ctx(cbox, w, h, **kw) as full, _ctx(cbox, w, h, **kw) as r0, _ctx(cbox, w, h, **kw) as r1:
+        full.render(8)
+        r0.render(4)
+        r1.set_first_sample(4)
+        r1.render(4)
+        s = full.read_sums()
+        m = r0.read_sums() + r1.read_sums()
+    assert np.array_equal(s[6], m[6])
+    np.testing.assert_allclose(m, s, rtol=1e-12)
+
+
+def test_error_paths(cbox):
+    with pytest.raises(device.McptError):
+        device.Context(0, 10, 8, 1)
+    with device.Context(16, 16, 8, 1) as ctx:
+        with pytest.raises(device.McptError):
+            ctx.render(1)                                   # no scene yet
+        with pytest.raises(device.McptError):
+            ctx.upload_scene(cbox.triangles, cbox.materials, cbox.nodes[:-1])
