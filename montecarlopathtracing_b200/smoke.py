@@ -22,6 +22,7 @@ def run():
             assert np.array_equal(closest, ref_closest), "closest-hit ids differ (traversal %d)" % trav
             for f in ("t", "material_id", "normal", "point"):
                 assert hits[f].tobytes() == ref_hits[f].tobytes(), "Hit.%s differs (traversal %d)" % (f, trav)
+        ctx.reset_stats()
         ctx.render(3)
         hist, counts = ctx.read_history()
         ref = O.render(sc.camera, W, H, sc.nodes, sc.triangles, sc.materials, 8, 4, 3, seed_mode=0, run_seed=7)

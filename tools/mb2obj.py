@@ -21,6 +21,7 @@ two ceiling faces and the reference's closest-hit rule is "first visited wins ti
 Usage: mb2obj.py in.mb out.obj --mtllib cbox.mtl [--first cbox_luminaire_mesh]
 """
 import argparse
+import os
 import re
 import struct
 import sys
@@ -107,6 +108,21 @@ def main():
                     help="substring of a mesh name to emit first (repeatable)")
     a = ap.parse_args()
     meshes, binds = recover(a.mb)
+    # usemtl must name a material of the .mtl exactly: the Maya file says "mis:plate_3" where the
+    # course's mis.mtl says "mi:plate_3", so names are matched on the part after the namespace colon.
+    mtl_names = []
+    mtl_path = os.path.join(os.path.dirname(os.path.abspath(a.obj)), a.mtllib)
+    if os.path.exists(mtl_path):
+        mtl_names = [l.split(None, 1)[1].strip() for l in open(mtl_path) if l.startswith("newmtl")]
+    def resolve(name):
+        if name is None or not mtl_names or name in mtl_names:
+            return name
+        tail = name.split(":")[-1]
+        cands = [m for m in mtl_names if m.split(":")[-1] == tail]
+        if not cands:
+            print("warning: material %s not in %s" % (name, a.mtllib), file=sys.stderr)
+            return name
+        return cands[0]
     def rank(m):
         for i, s in enumerate(a.first):
             if s in m[0] or s in (m[1] or ""):
@@ -125,6 +141,7 @@ def main():
             if mat is None:
                 cands = [v for k, v in binds.items() if k.split("|")[-1] == key]
                 mat = cands[0] if cands else None
+            mat = resolve(mat)
             if mat is None:
                 print("warning: no material bound to", shape, file=sys.stderr)
             f.write("g %s\n" % key)
