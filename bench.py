@@ -1,0 +1,325 @@
+#!/usr/bin/env python3
+"""bench.py — Mrays/s of the path-tracing loop (BASELINE.json metric) on N B200s of one node.
+
+Workload (config.workload): BASELINE configs[4], the headline target — Scene/diningroom (procedural
+stand-in, the reference ships no diningroom geometry) at 1920x1080, max depth 16.  One "step" = every
+rank renders `spp_per_step` more samples of the full frame with the fused wavefront pipeline
+(mcpt_render) and the per-pixel sums are merged onto rank 0 by ONE NCCL reduce (weak scaling: per-GPU
+work is fixed, ranks own disjoint sample indices, scene + BVH replicated).
+
+  value      Mrays/s, whole job, device-timed (CUDA events on the library's stream, max over ranks),
+             scene resident in HBM.
+  e2e        the same metric through the C ABI with HOST buffers: every step uploads the scene from
+             pinned host memory (mcpt_upload_scene + mcpt_set_camera), renders, and reads the merged
+             sums back to the host (mcpt_read_sums); wall clock around the calls.
+  roofline   the dominant kernel k_wave_bounce<FAST>: algorithmic bytes per ray (nodes and triangles
+             fetched, counted by an instrumented pass of the same kernel, x 64 B + 96 B path state)
+             x rays / summed CUDA-event time of the bounce launches, against the measured HBM copy
+             bandwidth (MEASURED_PEAKS.json).  The scene is L2-resident, so frac can exceed what HBM
+             traffic alone would allow; traffic (ncu dram bytes per launch) is read from profiles/.
+  cpu_baseline / --impl reference: the CPU oracle (a line-by-line port of the reference's OpenCL
+             kernels, which cannot be compiled here: no OpenCL platform, no clang) on all host cores,
+             on a bounded sample of the same workload (960x540, same camera/scene/depth).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (path-tracing loop, rays entering BVH traversal per second)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scene", default="diningroom")
+    ap.add_argument("--width", type=int, default=1920)
+    ap.add_argument("--height", type=int, default=1080)
+    ap.add_argument("--depth", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=8)
+    ap.add_argument("--samples-in-flight", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(a, n):
+    return {"workload": "Scene/%s%s %dx%d, max depth %d, %d spp per step per GPU, sample-index sharding"
+                        % (a.scene, " (procedural stand-in, 423792 triangles)" if a.scene == "diningroom" else "",
+                           a.width, a.height, a.depth, a.spp_per_step),
+            "scene": a.scene, "resolution": [a.width, a.height], "max_depth": a.depth,
+            "spp_per_step_per_gpu": a.spp_per_step, "parallelism": "sample-sharded x%d" % n,
+            "l2": "per-step path-state + sample streams (>=400 MB) exceed the 126 MB L2; scene is meant to stay L2-resident"}
+
+
+# ---------------------------------------------------------------------------- CPU side
+def ensure_built():
+    import __graft_entry__ as g
+    if not os.path.exists(os.path.join(ROOT, "oracle", "liboracle.so")):
+        g.build_oracle()
+    g.build_host()
+    g.build_assets()
+
+
+def cpu_sample(a, min_seconds=10.0, max_passes=8):
+    """Oracle (port of the reference kernels) on all host cores: 1-spp passes of a 960x540 view of the
+    same scene/camera/depth until min_seconds of work are done."""
+    from montecarlopathtracing_b200 import scenes
+    from oracle import oracle_api as O
+    sc = scenes.load(a.scene)
+    w, h = max(1, a.width // 2), max(1, a.height // 2)
+    rays = paths = 0
+    t0 = time.perf_counter()
+    passes = 0
+    while passes < max_passes and (passes == 0 or time.perf_counter() - t0 < min_seconds):
+        r = O.render(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, a.depth, 1 << 20, 1, seed_mode=1,
+                     run_seed=1, first_sample=passes)
+        rays += r["rays_traced"]
+        paths += w * h
+        passes += 1
+    dt = time.perf_counter() - t0
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": "%dx%d, %d spp, depth %d, same scene and camera (%.1f s of CPU work)" % (w, h, passes, a.depth, dt),
+            "mpaths_per_s": paths / dt / 1e6}, rays, paths, dt
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ensure_built()
+    for _ in range(min(a.warmup, 1)):
+        cpu_sample(a, min_seconds=0.0, max_passes=1)
+    tot_rays = tot_dt = tot_paths = 0
+    last = None
+    for _ in range(a.steps):
+        last, rays, paths, dt = cpu_sample(a, min_seconds=0.0, max_passes=1)
+        tot_rays += rays
+        tot_paths += paths
+        tot_dt += dt
+    v = tot_rays / tot_dt / 1e6
+    last.update(value=v, sample="%dx%d, 1 spp per step, depth %d, same scene and camera" % (a.width // 2, a.height // 2, a.depth),
+                mpaths_per_s=tot_paths / tot_dt / 1e6)
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": a.gpus,
+                      "steps": a.steps, "warmup": a.warmup, "ms_per_step": tot_dt / a.steps * 1e3,
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                      "data": "synthetic", "config": workload_config(a, a.gpus), "cpu_baseline": last,
+                      "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                      "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def read_json(path):
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
+
+
+# ---------------------------------------------------------------------------- GPU arm
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from montecarlopathtracing_b200 import device, scenes
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback for the product arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if rank == 0:
+        ensure_built()
+    if world > 1:
+        dist.barrier()
+
+    W, H, D, SPP = a.width, a.height, a.depth, a.spp_per_step
+    npix = W * H
+    sc = scenes.load(a.scene)
+    total_steps = a.warmup + a.steps + 2
+    ctx = device.Context(W, H, D, 1 << 30, device=local, seed_mode=1, run_seed=2024, samples_in_flight=a.samples_in_flight)
+    ctx.upload_scene(sc.triangles, sc.materials, sc.nodes)
+    ctx.set_camera(sc.camera)
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    sums = torch.zeros(7 * npix, dtype=torch.float64, device="cuda")
+    ctx.bind_sums(sums.data_ptr())
+    ctx.set_first_sample(rank * total_steps * SPP * 4)      # disjoint sample indices per rank
+
+    def merge():
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.reduce(sums, dst=0)
+                if rank != 0:
+                    sums.zero_()        # non-root ranks contribute deltas; rank 0 holds the merged frame
+
+    def step():
+        ctx.render_async(SPP)
+        merge()
+
+    def fence():
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---- instrumented pass: nodes / triangles fetched per ray by the same kernel (untimed)
+    ctx.set_profiling(count_fetches=True, time_bounces=False)
+    ctx.reset_stats()
+    ctx.render(1)
+    st = ctx.stats()
+    nodes_per_ray = st["nodes_fetched"] / max(1, st["rays_traced"])
+    tris_per_ray = st["tris_fetched"] / max(1, st["rays_traced"])
+    bytes_per_ray = nodes_per_ray * 64 + tris_per_ray * 64 + 96
+    ctx.set_profiling(count_fetches=False, time_bounces=True)
+
+    for _ in range(a.warmup):
+        step()
+    fence()
+    ctx.bounce_time()
+    ctx.reset_stats()
+    clocks = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(a.steps):
+        step()
+    e1.record(stream)
+    e1.synchronize()
+    fence()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if clocks else None
+    st = ctx.stats()
+    bounce_ms, bounce_launches = ctx.bounce_time()
+    t = torch.tensor([ms, bounce_ms], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([st["rays_traced"], st["paths"], st["kernel_launches"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    ms_max, bounce_ms_max = t.tolist()
+    rays, paths, launches = cnt.tolist()
+    value = rays / ms_max / 1e3
+
+    # ---- e2e through the C ABI with host buffers
+    ctx.set_profiling(False, False)
+    pin = lambda x: torch.from_numpy(np.ascontiguousarray(x).view(np.uint8).reshape(-1)).pin_memory().numpy().view(x.dtype)
+    h_tris, h_mats, h_nodes, h_cam = pin(sc.triangles), pin(sc.materials), pin(sc.nodes), pin(sc.camera)
+    h_out = torch.empty(7 * npix, dtype=torch.float64).pin_memory().numpy()
+    lib = device.lib()
+
+    def e2e_step():
+        ctx.upload_scene(h_tris, h_mats, h_nodes)
+        ctx.set_camera(h_cam)
+        ctx.render_async(SPP)
+        merge()
+        if rank == 0:
+            ctx._call("mcpt_read_sums", device._vp(h_out))
+        else:
+            ctx.synchronize()
+
+    e2e_step()
+    fence()
+    ctx.reset_stats()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        e2e_step()
+    fence()
+    e2e_s = time.perf_counter() - t0
+    st2 = ctx.stats()
+    t2 = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    c2 = torch.tensor([st2["rays_traced"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c2, op=dist.ReduceOp.SUM)
+    e2e_value = c2.item() / t2.item() / 1e6
+    h2d = sc.scene_bytes
+    d2h = 7 * 8 * npix
+
+    if rank == 0:
+        peaks = read_json(os.path.join(ROOT, "MEASURED_PEAKS.json"))
+        peak = float(peaks["hbm_gbs"]) if peaks and "hbm_gbs" in peaks else 6650.0
+        prof = read_json(os.path.join(ROOT, "profiles", "traffic.json")) or {}
+        achieved = bytes_per_ray * (rays / world) / (bounce_ms_max * 1e-3) / 1e9 if bounce_ms_max > 0 else None
+        out = {
+            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": workload_config(a, world),
+            "mpaths_per_s": paths / ms_max / 1e3, "rays_per_path": rays / max(1.0, paths),
+            "time_to_4096_spp_s": 4096.0 / (world * SPP) * (ms_max / a.steps) * 1e-3,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": t2.item() / a.steps * 1e3},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k_wave_bounce<FAST>", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
+                         "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                         "traffic": prof.get("dram_bytes_per_launch"),
+                         "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
+                         "kernel_ms_per_step": bounce_ms_max / a.steps, "kernel_launches": int(bounce_launches),
+                         "kernel_share_of_step": bounce_ms_max / ms_max,
+                         "note": "algorithmic bytes are served mostly by L1/L2 (scene is L2-resident)"},
+            "clocks": clk,
+        }
+        if world == 1 and not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_sample(a)[0]
+        print(json.dumps(out))
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -122,6 +122,13 @@ int mcpt_trace_device(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, mcpt_hit* d
 /* instrumented build of the same kernel: counts node and triangle records fetched (device buffers) */
 int mcpt_trace_count(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, int traversal);
 
+/* Measurement aids for bench.py (no effect on results):
+ *   count_fetches: the bounce kernels of mcpt_render also count node / triangle records fetched (slower);
+ *   time_bounces : CUDA events bracket every bounce-kernel launch on mcpt_stream(ctx); the summed device
+ *                  time and launch count since the last call are returned by mcpt_get_bounce_time. */
+int mcpt_set_profiling(mcpt_ctx* ctx, int count_fetches, int time_bounces);
+int mcpt_get_bounce_time(mcpt_ctx* ctx, double* ms, uint64_t* launches);
+
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);
 

@@ -31,6 +31,7 @@ struct DevBuf {
 	T* p = nullptr;
 	size_t n = 0;
 	cudaError_t alloc(size_t count) {
+		if (p && n == count) return cudaSuccess;     // same size: keep the allocation
 		release();
 		n = count;
 		return count ? cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T)) : cudaSuccess;
@@ -79,9 +80,28 @@ struct mcpt_ctx {
 	DevBuf<int32_t> t_closest;
 	uint64_t launches = 0;
 	uint64_t stage_paths = 0;
+	// measurement aids
+	bool count_fetches = false, time_bounces = false;
+	std::vector<cudaEvent_t> ev_pool;     // pairs (start, stop), ev_used of them recorded
+	size_t ev_used = 0;
+	double bounce_ms = 0.0;
+	uint64_t bounce_launches = 0;
 
 	~mcpt_ctx() {
+		for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
 		if (stream) cudaStreamDestroy(stream);
+	}
+	// fold recorded event pairs into bounce_ms (requires the stream to be idle)
+	cudaError_t drain_events() {
+		for (size_t k = 0; k + 1 < ev_used; k += 2) {
+			float ms = 0.f;
+			cudaError_t e = cudaEventElapsedTime(&ms, ev_pool[k], ev_pool[k + 1]);
+			if (e != cudaSuccess) return e;
+			bounce_ms += ms;
+			++bounce_launches;
+		}
+		ev_used = 0;
+		return cudaSuccess;
 	}
 	FrameDev frame() {
 		return FrameDev{rays.p, hits.p, closest.p, color.p, seeds.p, hist.p, counts.p, sums, npix};
@@ -150,11 +170,35 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int trav = c->traversal(c->prm.traversal);
+	const int g = blocks(total, 128);
+	unsigned long long* cnt = c->counters.p;
 	for (int d = 0; d < D; ++d) {
-		if (trav == MCPT_TRAVERSAL_REFERENCE)
-			k_wave_bounce<MCPT_TRAVERSAL_REFERENCE><<<blocks(total, 128), 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode);
-		else
-			k_wave_bounce<MCPT_TRAVERSAL_FAST><<<blocks(total, 128), 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode);
+		if (c->time_bounces) {
+			if (c->ev_used + 2 > c->ev_pool.size()) {
+				if (c->ev_pool.size() >= 8192) {       // bounded pool: drain (one sync) and reuse
+					CU(cudaStreamSynchronize(c->stream));
+					CU(c->drain_events());
+				} else {
+					cudaEvent_t a, b;
+					CU(cudaEventCreate(&a));
+					CU(cudaEventCreate(&b));
+					c->ev_pool.push_back(a);
+					c->ev_pool.push_back(b);
+				}
+			}
+			CU(cudaEventRecord(c->ev_pool[c->ev_used], c->stream));
+		}
+		if (trav == MCPT_TRAVERSAL_REFERENCE) {
+			if (c->count_fetches) k_wave_bounce<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
+			else k_wave_bounce<MCPT_TRAVERSAL_REFERENCE, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
+		} else {
+			if (c->count_fetches) k_wave_bounce<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
+			else k_wave_bounce<MCPT_TRAVERSAL_FAST, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
+		}
+		if (c->time_bounces) {
+			CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
+			c->ev_used += 2;
+		}
 	}
 	k_wave_resolve<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, nsamples, D, c->prm.max_attempt);
 	c->launches += uint64_t(D) + 2;
@@ -546,6 +590,26 @@ int mcpt_trace(mcpt_ctx* c, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_
 		if (closest) CU(cudaMemcpyAsync(closest + off, c->t_closest.p, sizeof(int32_t) * m, cudaMemcpyDeviceToHost, c->stream));
 	}
 	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_set_profiling(mcpt_ctx* c, int count_fetches, int time_bounces) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	CU(c->drain_events());
+	c->count_fetches = count_fetches != 0;
+	c->time_bounces = time_bounces != 0;
+	return MCPT_OK;
+}
+
+int mcpt_get_bounce_time(mcpt_ctx* c, double* ms, uint64_t* launches) {
+	if (int r = check_ctx(c, false, false)) return r;
+	CU(cudaStreamSynchronize(c->stream));
+	CU(c->drain_events());
+	if (ms) *ms = c->bounce_ms;
+	if (launches) *launches = c->bounce_launches;
+	c->bounce_ms = 0.0;
+	c->bounce_launches = 0;
 	return MCPT_OK;
 }
 

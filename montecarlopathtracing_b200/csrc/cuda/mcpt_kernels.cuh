@@ -172,8 +172,9 @@ __global__ void __launch_bounds__(256) k_wave_generate(CameraDev cam, WaveDev w,
 }
 
 // One bounce for every live path: closest hit + shade + (terminate | compact into the next queue).
-template <int TRAVERSAL>
-__global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode) {
+template <int TRAVERSAL, bool COUNT>
+__global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode,
+                                                      unsigned long long* counters) {
 	const int src = depth & 1, dst = src ^ 1;
 	const uint32_t total = w.qcount[depth];
 	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -192,8 +193,8 @@ __global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int
 		color = f4{c.x, c.y, c.z, 0.0f};
 		seed = uint32_t(__float_as_int(c.w));
 		HitRegs h{FLT_MAX, -1, 0, false};
-		if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<false>(sc, ray, tmin, h, nullptr, nullptr);
-		else trace_fast<false>(sc, ray, tmin, h, nullptr, nullptr);
+		if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+		else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
 		f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
 		uint32_t mat = 0;
 		if (h.closest >= 0) {

@@ -25,7 +25,7 @@ EXPORTS = [
     "mcpt_reset_accumulation", "mcpt_read_rays", "mcpt_write_rays", "mcpt_read_hits", "mcpt_write_hits",
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
-    "mcpt_reset_stats",
+    "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time",
 ]
 
 
@@ -240,6 +240,15 @@ class Context:
         s = Stats()
         self._call("mcpt_get_stats", ctypes.byref(s))
         return {k: getattr(s, k) for k, _ in Stats._fields_}
+
+    def set_profiling(self, count_fetches=False, time_bounces=False):
+        self._call("mcpt_set_profiling", int(count_fetches), int(time_bounces))
+
+    def bounce_time(self):
+        """(summed device ms of the bounce kernels, launches) since the last call; needs time_bounces."""
+        ms, n = ctypes.c_double(0), ctypes.c_uint64(0)
+        self._call("mcpt_get_bounce_time", ctypes.byref(ms), ctypes.byref(n))
+        return ms.value, n.value
 
     def reset_stats(self):
         self._call("mcpt_reset_stats")
