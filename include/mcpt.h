@@ -41,10 +41,14 @@ enum {
 
 /* Traversal algorithms.  Both return the reference's closest hit (SURVEY.md §8c definition). */
 enum {
-	MCPT_TRAVERSAL_REFERENCE = 0,  /* objdef.h:240-275 as written: 64 B nodes, one box per visit, no pruning,
-	                                   literal 4x4-cofactor arithmetic order; also reproduces Hit.triangleID (F7) */
-	MCPT_TRAVERSAL_FAST = 1        /* same canonical left-first leaf order, two-box nodes, conservative inner
-	                                   tests, exact leaf-box + triangle arithmetic, margin-guarded pruning */
+	MCPT_TRAVERSAL_REFERENCE = 0,  /* objdef.h:240-275 as written: 64 B nodes, one box per visit, left-first DFS, no
+	                                   pruning; also reproduces the raw Hit.triangleID field */
+	MCPT_TRAVERSAL_FAST = 1,       /* the product: near-child-first traversal with pruning on two-box nodes,
+	                                   conservative inner tests, exact leaf-box + triangle arithmetic, and the
+	                                   reference's accept rule replayed over the near-tie candidates in canonical
+	                                   order (proof sketch in csrc/cuda/mcpt_traverse.cuh) */
+	MCPT_TRAVERSAL_CANONICAL = 2   /* the reference's left-first leaf order on the two-box layout with margin-guarded
+	                                   pruning; fallback of FAST and a cross-check */
 };
 
 typedef struct mcpt_params {

@@ -57,7 +57,7 @@ struct mcpt_ctx {
 	DevBuf<mcpt_bvh_node> nodes_ref;
 	DevBuf<mcpt_triangle> tris_ref;
 	DevBuf<DNode> nodes;
-	DevBuf<DTri> tris;
+	DevBuf<DLeaf> leaves;
 	DevBuf<mcpt_material> mats;
 	DevBuf<float2> cs_table;
 	// reference-layout frame buffers (stage path)
@@ -124,6 +124,14 @@ struct mcpt_ctx {
 	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
 };
 
+// expands `stmt` with TRAV bound to the compile-time traversal id
+#define MCPT_DISPATCH_TRAVERSAL(trav, stmt)                                                     \
+	do {                                                                                        \
+		if ((trav) == MCPT_TRAVERSAL_REFERENCE) { constexpr int TRAV = MCPT_TRAVERSAL_REFERENCE; stmt; }      \
+		else if ((trav) == MCPT_TRAVERSAL_CANONICAL) { constexpr int TRAV = MCPT_TRAVERSAL_CANONICAL; stmt; } \
+		else { constexpr int TRAV = MCPT_TRAVERSAL_FAST; stmt; }                                \
+	} while (0)
+
 namespace {
 
 inline int blocks(long n, int bs) { return int((n + bs - 1) / bs); }
@@ -188,13 +196,10 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 			}
 			CU(cudaEventRecord(c->ev_pool[c->ev_used], c->stream));
 		}
-		if (trav == MCPT_TRAVERSAL_REFERENCE) {
-			if (c->count_fetches) k_wave_bounce<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
-			else k_wave_bounce<MCPT_TRAVERSAL_REFERENCE, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
-		} else {
-			if (c->count_fetches) k_wave_bounce<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
-			else k_wave_bounce<MCPT_TRAVERSAL_FAST, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt);
-		}
+		if (c->count_fetches)
+			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
+		else
+			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
 		if (c->time_bounces) {
 			CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
 			c->ev_used += 2;
@@ -210,15 +215,11 @@ int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hi
 	const int trav = c->traversal(traversal);
 	const int g = blocks(n, 128);
 	unsigned long long* cnt = c->counters.p;
-	if (trav == MCPT_TRAVERSAL_REFERENCE) {
-		if (count) k_intersect<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
-		else k_intersect<MCPT_TRAVERSAL_REFERENCE, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
-	} else if (trav == MCPT_TRAVERSAL_FAST) {
-		if (count) k_intersect<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
-		else k_intersect<MCPT_TRAVERSAL_FAST, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt);
-	} else {
-		return fail(MCPT_ERR_ARG, "unknown traversal");
-	}
+	if (trav < 0 || trav > 2) return fail(MCPT_ERR_ARG, "unknown traversal");
+	if (count)
+		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
+	else
+		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
 	++c->launches;
 	CU(cudaGetLastError());
 	return MCPT_OK;
@@ -302,11 +303,12 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
 		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
 	// ---- validate + derive the traversal layout (host side, once per scene)
-	std::vector<DTri> dt(ntris);
+	std::vector<DLeaf> dt(ntris);
+	std::memset(dt.data(), 0, dt.size() * sizeof(DLeaf));
 	for (int i = 0; i < ntris; ++i) {
 		const mcpt_triangle& t = tris[i];
 		if (t.material_id < 0 || t.material_id >= nmats) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
-		DTri& d = dt[i];
+		DLeaf& d = dt[i];
 		d.v0x = t.v[0].x; d.v0y = t.v[0].y; d.v0z = t.v[0].z; d.material = t.material_id;
 		// e1 = -(v1 - v0), e2 = -(v2 - v0): the matrix rows of objdef.h:194-199
 		d.e1x = -(t.v[1].x - t.v[0].x); d.e1y = -(t.v[1].y - t.v[0].y); d.e1z = -(t.v[1].z - t.v[0].z);
@@ -320,6 +322,33 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
 			return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
 	auto is_leaf = [&](int i) { return nodes[i].left == nodes[i].right; };
+	// canonical rank of every leaf = its position in the reference's left-first DFS (objdef.h:252-273);
+	// the leaf's box is copied from the reference leaf record (exact floats of the reference box test)
+	{
+		std::vector<int> st;
+		std::vector<char> seen(size_t(ntris), 0);
+		st.push_back(0);
+		int rank = 0;
+		long guard = 0;
+		while (!st.empty()) {
+			int i = st.back();
+			st.pop_back();
+			if (i < 0 || i >= nnodes || ++guard > 4L * nnodes) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: malformed node links");
+			if (is_leaf(i)) {
+				int t = nodes[i].left;
+				if (t < 0 || t >= ntris || seen[t]) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: leaf triangle index out of range or repeated");
+				seen[t] = 1;
+				DLeaf& d = dt[t];
+				d.rank = rank++;
+				d.bminx = nodes[i].bbmin.x; d.bminy = nodes[i].bbmin.y; d.bminz = nodes[i].bbmin.z;
+				d.bmaxx = nodes[i].bbmax.x; d.bmaxy = nodes[i].bbmax.y; d.bmaxz = nodes[i].bbmax.z;
+			} else {
+				st.push_back(nodes[i].right);
+				st.push_back(nodes[i].left);
+			}
+		}
+		if (rank != ntris) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: the node array does not reach every triangle exactly once");
+	}
 	bool contained = true;
 	const bool root_leaf = is_leaf(0);
 	std::vector<DNode> dn(root_leaf ? 1 : size_t(nnodes));   // indexed by reference node id (leaf slots unused)
@@ -356,18 +385,18 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	CU(c->nodes_ref.alloc(nnodes));
 	CU(c->tris_ref.alloc(ntris));
 	CU(c->nodes.alloc(dn.size()));
-	CU(c->tris.alloc(ntris));
+	CU(c->leaves.alloc(ntris));
 	CU(c->mats.alloc(nmats));
 	CU(c->cs_table.alloc(32768));
 	CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->nodes.p, dn.data(), sizeof(DNode) * dn.size(), cudaMemcpyHostToDevice, c->stream));
-	CU(cudaMemcpyAsync(c->tris.p, dt.data(), sizeof(DTri) * ntris, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->leaves.p, dt.data(), sizeof(DLeaf) * ntris, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->cs_table.p, cs.data(), sizeof(float2) * 32768, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	c->force_reference = !contained;
-	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->tris.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
 	c->have_scene = true;
 	return MCPT_OK;
 }
@@ -413,12 +442,8 @@ int mcpt_intersect(mcpt_ctx* c, int traversal) {
 	// the live-ray counter (counters[2]) feeds stats.rays_traced for the stage path
 	const int trav = c->traversal(traversal);
 	const int g = blocks(c->npix, 128);
-	if (trav == MCPT_TRAVERSAL_REFERENCE)
-		k_intersect<MCPT_TRAVERSAL_REFERENCE, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p);
-	else if (trav == MCPT_TRAVERSAL_FAST)
-		k_intersect<MCPT_TRAVERSAL_FAST, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p);
-	else
-		return fail(MCPT_ERR_ARG, "unknown traversal");
+	if (trav < 0 || trav > 2) return fail(MCPT_ERR_ARG, "unknown traversal");
+	MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p)));
 	++c->launches;
 	CU(cudaGetLastError());
 	return MCPT_OK;

@@ -11,6 +11,7 @@
 // which makes the running mean bit-identical to history.cl's frame-by-frame update.
 #pragma once
 
+#include "mcpt.h"
 #include "mcpt_traverse.cuh"
 
 namespace mcpt {
@@ -26,6 +27,13 @@ struct FrameDev {               // reference-layout per-pixel buffers (stage pat
 	double* sums;               // 7 planes of n doubles
 	int n;
 };
+
+template <int TRAVERSAL, bool COUNT>
+__device__ __forceinline__ void trace_dispatch(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& h, unsigned long long* counters) {
+	if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+	else if (TRAVERSAL == MCPT_TRAVERSAL_CANONICAL) trace_canonical<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+	else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+}
 
 __device__ __forceinline__ RayRegs load_ray(const mcpt_ray* rays, long i) {
 	const float4* p = reinterpret_cast<const float4*>(rays + i);
@@ -66,15 +74,14 @@ __global__ void __launch_bounds__(128) k_intersect(SceneDev sc, const mcpt_ray* 
 		if (!(state & MCPT_RAY_TERM_MASK)) {
 			live = true;
 			HitRegs h{FLT_MAX, -1, 0, false};
-			if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
-			else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+			trace_dispatch<TRAVERSAL, COUNT>(sc, ray, tmin, h, counters);
 			float4 nrm = make_float4(0, 0, 0, 0), pt = make_float4(0, 0, 0, 0);
 			uint32_t mat = 0;
 			if (h.closest >= 0) {
-				const float4* tp = reinterpret_cast<const float4*>(sc.tris + h.closest);
-				float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3);
-				f4 nn{q1.w, q2.w, q3.w, 0.0f};
-				mat = uint32_t(__float_as_int(q0.w));
+				const float4* tp = reinterpret_cast<const float4*>(sc.leaves + h.closest);
+				float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+				f4 nn{q2.w, q3.w, q4.w, 0.0f};
+				mat = uint32_t(__float_as_int(q1.w));
 				pt = st4(ray.origin + h.t * ray.direction);            // 4 lanes, like the float4 expression at objdef.h:218
 				if (h.any && dot3(ray.direction, nn) > 0) nn = -nn;    // intersect.cl:23-25
 				nrm = st4(nn);
@@ -193,15 +200,14 @@ __global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int
 		color = f4{c.x, c.y, c.z, 0.0f};
 		seed = uint32_t(__float_as_int(c.w));
 		HitRegs h{FLT_MAX, -1, 0, false};
-		if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
-		else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+		trace_dispatch<TRAVERSAL, COUNT>(sc, ray, tmin, h, counters);
 		f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
 		uint32_t mat = 0;
 		if (h.closest >= 0) {
-			const float4* tp = reinterpret_cast<const float4*>(sc.tris + h.closest);
-			float4 q0 = __ldg(tp), q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3);
-			nn = f4{q1.w, q2.w, q3.w, 0.0f};
-			mat = uint32_t(__float_as_int(q0.w));
+			const float4* tp = reinterpret_cast<const float4*>(sc.leaves + h.closest);
+			float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+			nn = f4{q2.w, q3.w, q4.w, 0.0f};
+			mat = uint32_t(__float_as_int(q1.w));
 			ip = ray.origin + h.t * ray.direction;
 			if (dot3(ray.direction, nn) > 0) nn = -nn;
 		}

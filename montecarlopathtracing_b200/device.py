@@ -16,7 +16,7 @@ from . import types as T
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-TRAVERSAL_REFERENCE, TRAVERSAL_FAST = 0, 1
+TRAVERSAL_REFERENCE, TRAVERSAL_FAST, TRAVERSAL_CANONICAL = 0, 1, 2
 
 EXPORTS = [
     "mcpt_last_error", "mcpt_abi_version", "mcpt_create", "mcpt_destroy", "mcpt_stream", "mcpt_synchronize",

@@ -5,10 +5,11 @@ import pytest
 
 from montecarlopathtracing_b200 import device, types as T
 from oracle import oracle_api as O
-from tests.util import hit_mismatches, hits_equal, random_rays
+from tests.util import adversarial_rays, hit_mismatches, hits_equal, random_rays
 
 pytestmark = pytest.mark.gpu
 
+ALL_TRAVERSALS = [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST, device.TRAVERSAL_CANONICAL]
 SCENE_RES = {"cbox": (256, 256), "mis": (320, 180)}
 
 
@@ -31,7 +32,7 @@ def test_generate_rays_bit_exact(name, request):
 
 
 @pytest.mark.parametrize("name", ["cbox", "mis"])
-@pytest.mark.parametrize("trav", [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST])
+@pytest.mark.parametrize("trav", ALL_TRAVERSALS)
 def test_primary_hits_bit_exact(name, trav, request):
     sc = request.getfixturevalue(name)
     w, h = SCENE_RES[name]
@@ -51,7 +52,7 @@ def test_primary_hits_bit_exact(name, trav, request):
 
 
 @pytest.mark.parametrize("name", ["cbox", "mis"])
-@pytest.mark.parametrize("trav", [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST])
+@pytest.mark.parametrize("trav", ALL_TRAVERSALS)
 def test_random_rays_bit_exact(name, trav, request):
     sc = request.getfixturevalue(name)
     rays = random_rays(200_000, sc.nodes)
@@ -60,6 +61,20 @@ def test_random_rays_bit_exact(name, trav, request):
         hits, closest = ctx.trace(rays, trav)
     assert np.array_equal(closest, ref_closest)
     assert hit_mismatches(hits, ref_hits) == 0
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_adversarial_rays_bit_exact(name, request):
+    """Rays aimed exactly at triangle vertices, edge midpoints and centroids (shared edges, coplanar
+    layers, grazing boxes): the tie situations where visit order decides the winner."""
+    sc = request.getfixturevalue(name)
+    rays = adversarial_rays(sc, 60_000)
+    ref_hits, ref_closest = O.intersect(rays, sc.nodes, sc.triangles)
+    with _ctx(sc, 64, 64) as ctx:
+        for trav in ALL_TRAVERSALS:
+            hits, closest = ctx.trace(rays, trav)
+            assert np.array_equal(closest, ref_closest), trav
+            assert hit_mismatches(hits, ref_hits) == 0, trav
 
 
 def test_trace_edge_cases(cbox):
@@ -72,7 +87,7 @@ def test_trace_edge_cases(cbox):
         rays["direction"][::13] = (0.0, 0.0, 1.0)
         rays["state"][::5] = np.int32(-16777216)                 # terminated rays: hit record left untouched
         ref_hits, ref_closest = O.intersect(rays, cbox.nodes, cbox.triangles)
-        for trav in (device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST):
+        for trav in ALL_TRAVERSALS:
             hits, closest = ctx.trace(rays, trav)
             live = (rays["state"].view(np.uint32) & T.RAY_TERM_MASK) == 0
             assert np.array_equal(closest, ref_closest)

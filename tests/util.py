@@ -31,3 +31,27 @@ def hit_mismatches(a, b, fields=("t", "material_id", "normal", "point")):
         y = b[f].view(np.uint32).reshape(len(b), -1)
         bad |= (x != y).any(axis=1)
     return int(bad.sum())
+
+
+def adversarial_rays(sc, n, seed=77):
+    """Origins uniform in the scene box, aimed EXACTLY (in float) at triangle vertices, edge midpoints and
+    centroids, so hits land on shared edges/vertices and coplanar layers."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    nodes, tris = sc.nodes, sc.triangles
+    lo = nodes["bbmin"][0][:3].astype(np.float64)
+    hi = nodes["bbmax"][0][:3].astype(np.float64)
+    t = rng.integers(0, len(tris), n)
+    v = tris["v"][t][:, :, :3].astype(np.float64)          # (n, 3 verts, xyz)
+    kind = rng.integers(0, 3, n)
+    a = rng.integers(0, 3, n)
+    idx = np.arange(n)
+    target = np.where((kind == 0)[:, None], v[idx, a],
+                      np.where((kind == 1)[:, None], 0.5 * (v[idx, a] + v[idx, (a + 1) % 3]), v.mean(axis=1)))
+    org = (lo + (hi - lo) * rng.random((n, 3))).astype(np.float32)
+    d = target.astype(np.float32) - org
+    d = d / np.maximum(np.linalg.norm(d, axis=1, keepdims=True), 1e-20)
+    rays = np.zeros(n, T.RAY)
+    rays["origin"] = org
+    rays["direction"] = d.astype(np.float32)
+    rays["pixel"] = np.arange(n, dtype=np.int32)
+    return rays

@@ -39,7 +39,7 @@ def main():
             for label, rays in (("coherent", prim), ("random", rnd)):
                 d_rays = torch.from_numpy(rays.view(np.uint8)).cuda()
                 res = {}
-                for trav, tn in ((0, "reference"), (1, "fast")):
+                for trav, tn in ((0, "reference"), (2, "canonical"), (1, "fast")):
                     ms = time_trace(ctx, d_rays, n, d_hits, d_closest, trav)
                     st = ctx.trace_count(d_rays.data_ptr(), n, trav)
                     res[tn] = d_closest.cpu().numpy().copy() if False else None
