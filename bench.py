@@ -163,7 +163,7 @@ def read_json(path):
 def run_b200(a):
     import torch
     import torch.distributed as dist
-    from montecarlopathtracing_b200 import device, scenes
+    from montecarlopathtracing_b200 import device, scenes, sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -194,9 +194,7 @@ def run_b200(a):
     def merge():
         if world > 1:
             with torch.cuda.stream(stream):
-                dist.reduce(sums, dst=0)
-                if rank != 0:
-                    sums.zero_()        # non-root ranks contribute deltas; rank 0 holds the merged frame
+                sharding.merge_sums(sums, 0)    # non-root ranks contribute deltas; rank 0 holds the merged frame
 
     def step():
         ctx.render_async(SPP)

@@ -46,6 +46,7 @@ struct Parser {
 			if (eat('}')) return j;
 			do {
 				skip();
+				if (p < s.size() && s[p] == '}') break;     // trailing comma (the shipped config.json has one once its '#' lines are dropped)
 				if (p >= s.size() || s[p] != '"') fail("expected key string");
 				std::string k = string_body();
 				if (!eat(':')) fail("expected ':'");
@@ -56,7 +57,11 @@ struct Parser {
 			++p;
 			j.kind = Json::Array;
 			if (eat(']')) return j;
-			do { j.arr.push_back(value()); } while (eat(','));
+			do {
+				skip();
+				if (p < s.size() && s[p] == ']') break;     // trailing comma
+				j.arr.push_back(value());
+			} while (eat(','));
 			if (!eat(']')) fail("expected ']'");
 		} else if (c == '"') {
 			j.kind = Json::String;

@@ -189,3 +189,34 @@ def test_error_paths(cbox):
             ctx.render(1)                                   # no scene yet
         with pytest.raises(device.McptError):
             ctx.upload_scene(cbox.triangles, cbox.materials, cbox.nodes[:-1])
+
+
+@pytest.mark.parametrize("name,file", [("cbox", "cbox_primary.npz"), ("mis", "mis_primary.npz")])
+def test_primary_hits_match_golden_fixture(name, file, request):
+    """The committed golden vectors (generated in the build container) through the C ABI."""
+    import os
+    sc = request.getfixturevalue(name)
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", file))
+    w, h = int(g["width"]), int(g["height"])
+    with _ctx(sc, w, h) as ctx:
+        for trav in ALL_TRAVERSALS:
+            ctx.generate_rays()
+            ctx.intersect(trav)
+            hits, closest = ctx.read_hits()
+            assert np.array_equal(closest, g["closest"])
+            assert np.array_equal(hits["t"].view(np.uint32), g["t_bits"])
+            assert np.array_equal(hits["material_id"], g["material"])
+            assert np.array_equal(hits["normal"].view(np.uint32), g["normal_bits"])
+            assert np.array_equal(hits["point"].view(np.uint32), g["point_bits"])
+
+
+def test_render_matches_golden_fixture(cbox):
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "cbox_render.npz"))
+    for mode in (0, 1):
+        with _ctx(cbox, 24, 24, max_depth=8, max_attempt=5, seed_mode=mode, run_seed=11, samples_in_flight=3) as ctx:
+            ctx.render(6)
+            hist, counts = ctx.read_history()
+            assert np.array_equal(hist.view(np.uint32), g["hist_bits_%d" % mode])
+            assert np.array_equal(counts, g["counts_%d" % mode])
+            assert ctx.stats()["rays_traced"] == int(g["rays_%d" % mode])
