@@ -1,0 +1,162 @@
+// mcpt — headless command-line renderer: the reference's main.cpp / OpenCLApp.cpp with the OpenCL layer
+// replaced by the CUDA C ABI (include/mcpt.h) and the GLUT window replaced by file output.
+//
+//   reference                               here
+//   Config::CONFIG()        config.cpp:70   mcpt_host_load_config(./config.json or --config, --configid)
+//   OpenCL::init()          OpenCLApp.cpp:36 App::init(): loadObject -> HLBVH -> mcpt_create/upload/set_camera
+//   OpenCL::update()        OpenCLApp.cpp:57 App::update(): mcpt_render(batch) (one call renders many frames)
+//   ColorOut (attempt+1 frames, then <objname>.hdr) colorout.cpp:55-68   the loop in main(); also <objname>.png
+//
+// Multi-GPU (--gpus N, one host thread per device): each device renders a contiguous block of sample indices
+// (seed_mode 1) into its own accumulators; the sums are merged on the host at the end.  The torchrun path
+// (bench.py) merges with one NCCL reduce instead.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "mcpt.h"
+#include "mcpt_host.h"
+
+namespace MCPT {
+namespace App {
+
+struct State {
+	mcpt_host_config cfg{};
+	mcpt_triangle* tris = nullptr;
+	mcpt_material* mats = nullptr;
+	int* mat_ids = nullptr;
+	int ntris = 0, nmats = 0;
+	std::vector<mcpt_bvh_node> nodes;
+	std::vector<mcpt_ctx*> ctx;
+	int spp = 0;             // config "attempt"
+	uint32_t run_seed = 1;
+	bool reference_seeding = true;
+};
+
+[[noreturn]] void die(const char* what, const char* detail) {
+	std::fprintf(stderr, "mcpt: %s: %s\n", what, detail ? detail : "");
+	std::exit(1);
+}
+
+void init(State& s, int ngpus) {
+	if (!s.cfg.opencl) die("config", "Not Implemented");            // raygeneration.cpp:36-38 throws the same
+	if (mcpt_host_load_object(s.cfg.directory, s.cfg.objname, 1, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
+		die("loadObject", mcpt_host_last_error());
+	s.nodes.resize(size_t(2 * s.ntris - 1));
+	if (mcpt_host_build_bvh(s.tris, s.ntris, s.cfg.bvhtype, s.nodes.data()) < 0) die("BVH", mcpt_host_last_error());
+	if (!s.cfg.has_camera) die("config", "no camera");
+	if (s.cfg.res_x != s.cfg.width || s.cfg.res_y != s.cfg.height)
+		die("config", "camera.resolution must equal width/height (SURVEY A.5)");
+	for (int g = 0; g < ngpus; ++g) {
+		mcpt_params p{};
+		p.width = s.cfg.width;
+		p.height = s.cfg.height;
+		p.max_depth = s.cfg.maxdepth;
+		p.max_attempt = s.cfg.attempt;
+		p.device = g;
+		p.seed_mode = (ngpus > 1 || !s.reference_seeding) ? 1 : 0;
+		p.run_seed = s.run_seed;
+		p.traversal = MCPT_TRAVERSAL_FAST;
+		mcpt_ctx* c = mcpt_create(&p);
+		if (!c) die("mcpt_create", mcpt_last_error());
+		if (mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size())) ||
+		    mcpt_set_camera(c, &s.cfg.camera))
+			die("scene upload", mcpt_last_error());
+		s.ctx.push_back(c);
+	}
+}
+
+// Renders `frames` more frames on every device (device g takes its share of the sample indices).
+void update(State& s, int first_frame, int frames) {
+	const int G = int(s.ctx.size());
+	std::vector<std::thread> th;
+	for (int g = 0; g < G; ++g) {
+		int base = frames / G, rem = frames % G;
+		int count = base + (g < rem ? 1 : 0);
+		int first = first_frame + g * base + (g < rem ? g : rem);
+		th.emplace_back([&, g, first, count] {
+			if (G > 1 && mcpt_set_first_sample(s.ctx[g], uint32_t(first))) die("mcpt_set_first_sample", mcpt_last_error());
+			if (mcpt_render(s.ctx[g], count)) die("mcpt_render", mcpt_last_error());
+		});
+	}
+	for (auto& t : th) t.join();
+}
+
+}  // namespace App
+}  // namespace MCPT
+
+int main(int argc, char** argv) {
+	using namespace MCPT::App;
+	std::string config = "./config.json", out_prefix;
+	int configid = -1, gpus = 1, spp_override = -1, batch = 64;
+	State s;
+	for (int i = 1; i < argc; ++i) {
+		std::string a = argv[i];
+		auto next = [&]() -> const char* { if (i + 1 >= argc) die("missing value for", a.c_str()); return argv[++i]; };
+		if (a == "--config") config = next();
+		else if (a == "--configid") configid = std::atoi(next());
+		else if (a == "--gpus") gpus = std::atoi(next());
+		else if (a == "--spp") spp_override = std::atoi(next());
+		else if (a == "--out") out_prefix = next();
+		else if (a == "--seed") s.run_seed = uint32_t(std::strtoul(next(), nullptr, 10));
+		else if (a == "--batch") batch = std::atoi(next());
+		else if (a == "--order-independent-seeds") s.reference_seeding = false;
+		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch)", a.c_str());
+	}
+	if (mcpt_host_load_config(config.c_str(), configid, &s.cfg) < 0) die("config", mcpt_host_last_error());
+	if (s.cfg.testall || s.cfg.testbvh) die("config", "testbvh/testall (BVH quality harness) is out of scope of this build");
+	if (spp_override >= 0) s.cfg.attempt = spp_override;
+	if (gpus < 1) gpus = 1;
+	auto t0 = std::chrono::steady_clock::now();
+	init(s, gpus);
+	auto t1 = std::chrono::steady_clock::now();
+	// the reference accumulates while attemptCount <= attempt, i.e. attempt + 1 frames (colorout.cpp:55-62)
+	const int frames = s.cfg.attempt + 1;
+	for (int done = 0; done < frames;) {
+		int n = std::min(batch * gpus, frames - done);
+		update(s, done, n);
+		done += n;
+	}
+	auto t2 = std::chrono::steady_clock::now();
+	const size_t npix = size_t(s.cfg.width) * size_t(s.cfg.height);
+	std::vector<float> img(4 * npix, 0.0f);
+	mcpt_stats tot{};
+	if (gpus == 1) {
+		if (mcpt_read_history(s.ctx[0], img.data(), nullptr)) die("readback", mcpt_last_error());
+		mcpt_get_stats(s.ctx[0], &tot);
+	} else {
+		std::vector<double> acc(7 * npix, 0.0), part(7 * npix);
+		for (mcpt_ctx* c : s.ctx) {
+			if (mcpt_read_sums(c, part.data())) die("readback", mcpt_last_error());
+			for (size_t k = 0; k < acc.size(); ++k) acc[k] += part[k];
+			mcpt_stats st{};
+			mcpt_get_stats(c, &st);
+			tot.rays_traced += st.rays_traced;
+			tot.paths += st.paths;
+		}
+		for (size_t p = 0; p < npix; ++p) {
+			double n = acc[6 * npix + p] > 0 ? acc[6 * npix + p] : 1.0;
+			for (int k = 0; k < 3; ++k) img[4 * p + k] = float(acc[k * npix + p] / n);
+		}
+	}
+	std::string base = out_prefix.empty() ? std::string(s.cfg.objname) : out_prefix;
+	if (mcpt_host_write_hdr((base + ".hdr").c_str(), s.cfg.width, s.cfg.height, img.data()) < 0 ||
+	    mcpt_host_write_png((base + ".png").c_str(), s.cfg.width, s.cfg.height, img.data()) < 0)
+		die("outputPicture", mcpt_host_last_error());
+	double sec = std::chrono::duration<double>(t2 - t1).count();
+	std::printf("Finished Attempting\n");                                    // colorout.cpp:65
+	std::printf("{\"scene\": \"%s%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"gpus\": %d, \"init_s\": %.3f, "
+	            "\"render_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
+	            s.cfg.directory, s.cfg.objname, s.cfg.width, s.cfg.height, frames, gpus,
+	            std::chrono::duration<double>(t1 - t0).count(), sec, tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
+	for (mcpt_ctx* c : s.ctx) mcpt_destroy(c);
+	mcpt_host_free(s.tris);
+	mcpt_host_free(s.mats);
+	mcpt_host_free(s.mat_ids);
+	return 0;
+}

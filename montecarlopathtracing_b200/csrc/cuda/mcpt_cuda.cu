@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "mcpt.h"
+#include "accel_build.hpp"
 #include "mcpt_kernels.cuh"
 
 using namespace mcpt;
@@ -56,7 +57,7 @@ struct mcpt_ctx {
 	// scene
 	DevBuf<mcpt_bvh_node> nodes_ref;
 	DevBuf<mcpt_triangle> tris_ref;
-	DevBuf<DNode> nodes;
+	DevBuf<DNode> nodes, fast_nodes;
 	DevBuf<DLeaf> leaves;
 	DevBuf<mcpt_material> mats;
 	DevBuf<float2> cs_table;
@@ -381,7 +382,12 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		float deg = float(2 * 3.14159265358979323846 / 32768 * double(uint32_t(r)));
 		cs[r] = make_float2(float(std::cos(double(deg))), float(std::sin(double(deg))));
 	}
+	std::vector<DNode> fast;
+	if (!root_leaf) build_sah_bvh2(dt.data(), ntris, fast);
+	else fast.assign(1, DNode{});
 	CU(cudaStreamSynchronize(c->stream));
+	CU(c->fast_nodes.alloc(fast.size()));
+	CU(cudaMemcpyAsync(c->fast_nodes.p, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
 	CU(c->nodes_ref.alloc(nnodes));
 	CU(c->tris_ref.alloc(ntris));
 	CU(c->nodes.alloc(dn.size()));
@@ -396,7 +402,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	CU(cudaMemcpyAsync(c->cs_table.p, cs.data(), sizeof(float2) * 32768, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	c->force_reference = !contained;
-	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
 	c->have_scene = true;
 	return MCPT_OK;
 }

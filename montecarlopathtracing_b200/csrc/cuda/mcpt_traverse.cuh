@@ -20,36 +20,16 @@
 //                    walk instead.
 #pragma once
 
+#include "accel_layout.hpp"
 #include "mcpt_device.cuh"
 
 namespace mcpt {
 
-// Derived node: both children's boxes + child references.  ref >= 0: inner node index; ref < 0: ~triangle.
-struct __align__(16) DNode {
-	float lminx, lminy, lminz, lmaxx;
-	float lmaxy, lmaxz, rminx, rminy;
-	float rminz, rmaxx, rmaxy, rmaxz;
-	int32_t left, right, pad0, pad1;
-};
-static_assert(sizeof(DNode) == 64, "DNode");
-
-// Leaf record: the leaf's box (the exact floats of the reference leaf node), the canonical rank of the
-// leaf (its position in the reference's left-first DFS leaf order) and everything the exact triangle test
-// needs, 6 x 16 B.
-struct __align__(16) DLeaf {
-	float bminx, bminy, bminz; int32_t rank;
-	float bmaxx, bmaxy, bmaxz; int32_t material;
-	float v0x, v0y, v0z, nx;
-	float e1x, e1y, e1z, ny;       // e1 = -(v1 - v0)
-	float e2x, e2y, e2z, nz;       // e2 = -(v2 - v0)
-	float cr0, cr1, cr2, pad;      // ray-independent 2x2 determinants of (e1, e2)
-};
-static_assert(sizeof(DLeaf) == 96, "DLeaf");
-
 struct SceneDev {
 	const mcpt_bvh_node* nodes_ref;
 	const mcpt_triangle* tris_ref;
-	const DNode* nodes;
+	const DNode* nodes;          // reference topology, two-box layout (canonical walk)
+	const DNode* fast_nodes;     // SAH tree over the same leaves (fast walk)
 	const DLeaf* leaves;
 	const mcpt_material* materials;
 	const float2* cs_table;
@@ -295,7 +275,7 @@ __device__ __forceinline__ void trace_fast(const SceneDev& sc, const RayRegs& ra
 	while (cur != DONE) {
 		// ---- inner nodes: conservative tests of both children, near child first
 		while (cur >= 0 && cur != DONE) {
-			const float4* p = reinterpret_cast<const float4*>(sc.nodes + cur);
+			const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
 			float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
 			int4 link = __ldg(reinterpret_cast<const int4*>(p + 3));
 			if (COUNT) ++ln;
