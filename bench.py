@@ -77,6 +77,7 @@ def cpu_sample(a, min_seconds=10.0, max_passes=8):
     from montecarlopathtracing_b200 import scenes
     from oracle import oracle_api as O
     sc = scenes.load(a.scene)
+    cores = O.set_threads()              # all host cores, even under torchrun's OMP_NUM_THREADS=1
     w, h = max(1, a.width // 2), max(1, a.height // 2)
     rays = paths = 0
     t0 = time.perf_counter()
@@ -88,7 +89,7 @@ def cpu_sample(a, min_seconds=10.0, max_passes=8):
         paths += w * h
         passes += 1
     dt = time.perf_counter() - t0
-    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "port",
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
             "sample": "%dx%d, %d spp, depth %d, same scene and camera (%.1f s of CPU work)" % (w, h, passes, a.depth, dt),
             "mpaths_per_s": paths / dt / 1e6}, rays, paths, dt
 

@@ -34,6 +34,7 @@
 #include <cstdint>
 #include <cstring>
 #include <vector>
+#include <omp.h>
 
 #include "../include/mcpt_types.h"
 
@@ -407,6 +408,9 @@ inline uint32_t sample_seed(uint32_t pixel, uint32_t sample, uint32_t run_seed) 
 extern "C" {
 
 int oracle_abi_version(void) { return 1; }
+// torchrun exports OMP_NUM_THREADS=1; the timed CPU baseline asks for all host cores explicitly.
+void oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int oracle_max_threads(void) { return omp_get_max_threads(); }
 
 void oracle_generate_rays(const mcpt_camera* cam, int width, int height, mcpt_ray* rays) {
 #pragma omp parallel for schedule(static)

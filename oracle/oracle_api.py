@@ -100,3 +100,10 @@ def render(camera, width, height, nodes, tris, materials, max_depth, max_attempt
                            frames, seed_mode, ctypes.c_uint32(run_seed), ctypes.c_uint32(first_sample),
                            ctypes.c_float(tmin), _vp(hist), _vp(counts), _vp(s), _vp(s2), ctypes.byref(traced))
     return {"hist": hist, "counts": counts, "sum": s, "sumsq": s2, "rays_traced": traced.value}
+
+
+def set_threads(n=None):
+    """Use n OpenMP threads (default: all host cores) regardless of OMP_NUM_THREADS; returns the count in effect."""
+    L = oracle()
+    L.oracle_set_threads(int(n or os.cpu_count() or 1))
+    return L.oracle_max_threads()
