@@ -79,6 +79,8 @@ struct mcpt_ctx {
 	DevBuf<mcpt_ray> t_rays;
 	DevBuf<mcpt_hit> t_hits;
 	DevBuf<int32_t> t_closest;
+	std::vector<mcpt_triangle> cache_tris;   // host copy of the last upload (derived-layout cache key)
+	std::vector<mcpt_bvh_node> cache_nodes;
 	uint64_t launches = 0;
 	uint64_t stage_paths = 0;
 	// measurement aids
@@ -303,6 +305,26 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	if (int r = check_ctx(c, false, false)) return r;
 	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
 		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
+	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
+	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
+	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
+	    std::memcmp(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
+	    std::memcmp(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
+		for (int m = 0; m < nmats; ++m)
+			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
+				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
+		for (int i = 0; i < ntris; ++i)
+			if (tris[i].material_id < 0 || tris[i].material_id >= nmats)
+				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
+		CU(cudaStreamSynchronize(c->stream));
+		CU(c->mats.alloc(nmats));
+		CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaStreamSynchronize(c->stream));
+		c->scene.materials = c->mats.p;
+		return MCPT_OK;
+	}
 	// ---- validate + derive the traversal layout (host side, once per scene)
 	std::vector<DLeaf> dt(ntris);
 	std::memset(dt.data(), 0, dt.size() * sizeof(DLeaf));
@@ -402,6 +424,8 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	CU(cudaMemcpyAsync(c->cs_table.p, cs.data(), sizeof(float2) * 32768, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	c->force_reference = !contained;
+	c->cache_tris.assign(tris, tris + ntris);
+	c->cache_nodes.assign(nodes, nodes + nnodes);
 	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
 	c->have_scene = true;
 	return MCPT_OK;

@@ -280,6 +280,9 @@ __device__ __forceinline__ void trace_fast(const SceneDev& sc, const RayRegs& ra
 			int4 link = __ldg(reinterpret_cast<const int4*>(p + 3));
 			if (COUNT) ++ln;
 			const float tprune = best * PRUNE_REL + PRUNE_ABS;
+			// (bb - o) * (1/d): |computed - reference| <= 2^-22 |t|, covered 4x by the 2^-20 relative slack.  (A single
+			// fused bb*(1/d) - o*(1/d) is cheaper but its error scales with |o/d|: rays nearly parallel to an axis
+			// would then accept every box - measured 3x slower on random rays, so it is not used.)
 			float o1, o2, n0, n1, n2, f0, f1, f2;
 			o1 = (a.x - ray.origin.x) * rx; o2 = (a.w - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
 			o1 = (a.y - ray.origin.y) * ry; o2 = (b.x - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
