@@ -43,12 +43,15 @@ enum {
 enum {
 	MCPT_TRAVERSAL_REFERENCE = 0,  /* objdef.h:240-275 as written: 64 B nodes, one box per visit, left-first DFS, no
 	                                   pruning; also reproduces the raw Hit.triangleID field */
-	MCPT_TRAVERSAL_FAST = 1,       /* the product: near-child-first traversal with pruning on two-box nodes,
-	                                   conservative inner tests, exact leaf-box + triangle arithmetic, and the
-	                                   reference's accept rule replayed over the near-tie candidates in canonical
-	                                   order (proof sketch in csrc/cuda/mcpt_traverse.cuh) */
-	MCPT_TRAVERSAL_CANONICAL = 2   /* the reference's left-first leaf order on the two-box layout with margin-guarded
+	MCPT_TRAVERSAL_FAST = 1,       /* the product: near-child-first traversal with pruning on a binary SAH tree with
+	                                   two-box nodes, conservative inner tests, certified leaf-box + triangle decisions
+	                                   (exact reference arithmetic whenever a decision is close), and the reference's
+	                                   accept rule replayed over the near-tie candidates in canonical order (proof
+	                                   sketch in csrc/cuda/mcpt_traverse.cuh) */
+	MCPT_TRAVERSAL_CANONICAL = 2,  /* the reference's left-first leaf order on the two-box layout with margin-guarded
 	                                   pruning; fallback of FAST and a cross-check */
+	MCPT_TRAVERSAL_WIDE8 = 3       /* experimental: FAST's algorithm on 8-wide nodes with 8-bit quantised child boxes
+	                                   (80 B per 8 children); same answers, measured slower than FAST on B200 (r1) */
 };
 
 typedef struct mcpt_params {
@@ -70,8 +73,9 @@ typedef struct mcpt_stats {
 	uint64_t rays_traced;     /* live rays that entered an intersect stage since create/reset (Mrays/s numerator) */
 	uint64_t paths;           /* pixel samples finished by mcpt_render / mcpt_frame (Mpaths/s numerator) */
 	uint64_t kernel_launches; /* CUDA kernels launched by this context */
-	uint64_t nodes_fetched;   /* only filled by mcpt_trace_count */
-	uint64_t tris_fetched;
+	uint64_t nodes_fetched;   /* inner-node records fetched (instrumented kernels only: mcpt_trace_count, profiling) */
+	uint64_t tris_fetched;    /* exact triangle tests */
+	uint64_t leaves_fetched;  /* leaf records fetched (FAST / ORDERED2; the other walks read leaf boxes from nodes) */
 } mcpt_stats;
 
 const char* mcpt_last_error(void);

@@ -1,6 +1,8 @@
 // libmcpt_cuda.so — context management and the C ABI of include/mcpt.h (sm_100a only, no CPU fallback).
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -58,7 +60,8 @@ struct mcpt_ctx {
 	DevBuf<mcpt_bvh_node> nodes_ref;
 	DevBuf<mcpt_triangle> tris_ref;
 	DevBuf<DNode> nodes, fast_nodes;
-	DevBuf<DLeaf> leaves;
+	DevBuf<DLeaf> leaves, wleaves;
+	DevBuf<WNode> wnodes;
 	DevBuf<mcpt_material> mats;
 	DevBuf<float2> cs_table;
 	// reference-layout frame buffers (stage path)
@@ -79,6 +82,7 @@ struct mcpt_ctx {
 	DevBuf<mcpt_ray> t_rays;
 	DevBuf<mcpt_hit> t_hits;
 	DevBuf<int32_t> t_closest;
+	int opt_flags = 0, block = 128;          // development switches: env MCPT_OPT, MCPT_BLOCK
 	std::vector<mcpt_triangle> cache_tris;   // host copy of the last upload (derived-layout cache key)
 	std::vector<mcpt_bvh_node> cache_nodes;
 	uint64_t launches = 0;
@@ -132,6 +136,7 @@ struct mcpt_ctx {
 	do {                                                                                        \
 		if ((trav) == MCPT_TRAVERSAL_REFERENCE) { constexpr int TRAV = MCPT_TRAVERSAL_REFERENCE; stmt; }      \
 		else if ((trav) == MCPT_TRAVERSAL_CANONICAL) { constexpr int TRAV = MCPT_TRAVERSAL_CANONICAL; stmt; } \
+		else if ((trav) == MCPT_TRAVERSAL_WIDE8) { constexpr int TRAV = MCPT_TRAVERSAL_WIDE8; stmt; }   \
 		else { constexpr int TRAV = MCPT_TRAVERSAL_FAST; stmt; }                                \
 	} while (0)
 
@@ -181,7 +186,8 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int trav = c->traversal(c->prm.traversal);
-	const int g = blocks(total, 128);
+	const int BS = c->block;
+	const int g = blocks(total, BS);
 	unsigned long long* cnt = c->counters.p;
 	for (int d = 0; d < D; ++d) {
 		if (c->time_bounces) {
@@ -200,9 +206,9 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 			CU(cudaEventRecord(c->ev_pool[c->ev_used], c->stream));
 		}
 		if (c->count_fetches)
-			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
+			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, true><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
 		else
-			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, false><<<g, 128, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
+			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, false><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
 		if (c->time_bounces) {
 			CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
 			c->ev_used += 2;
@@ -216,13 +222,14 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 
 int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal, bool count) {
 	const int trav = c->traversal(traversal);
-	const int g = blocks(n, 128);
+	const int BS = c->block;
+	const int g = blocks(n, BS);
 	unsigned long long* cnt = c->counters.p;
-	if (trav < 0 || trav > 2) return fail(MCPT_ERR_ARG, "unknown traversal");
+	if (trav < 0 || trav > 3) return fail(MCPT_ERR_ARG, "unknown traversal");
 	if (count)
-		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
+		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, BS, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
 	else
-		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, false><<<g, 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
+		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, false><<<g, BS, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
 	++c->launches;
 	CU(cudaGetLastError());
 	return MCPT_OK;
@@ -263,6 +270,8 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	if (c->prm.tmin == 0.0f) c->prm.tmin = 0.001f;
 	if (c->prm.seed_mode == 0) c->prm.samples_in_flight = 1;
 	c->npix = params->width * params->height;
+	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
+	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128 || b == 256) c->block = b; }
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
 	ok = ok && c->rays.alloc(n) == cudaSuccess && c->hits.alloc(n) == cudaSuccess && c->closest.alloc(n) == cudaSuccess &&
@@ -340,6 +349,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		d.cr1 = d.e1x * d.e2z - d.e2x * d.e1z;
 		d.cr2 = d.e1x * d.e2y - d.e2x * d.e1y;
 		d.nx = t.nx; d.ny = t.ny; d.nz = t.nz;
+		std::memcpy(&d.pad, &i, sizeof(int));     // own index: leaf records are self-describing in any order
 	}
 	for (int m = 0; m < nmats; ++m)
 		if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
@@ -407,7 +417,15 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	std::vector<DNode> fast;
 	if (!root_leaf) build_sah_bvh2(dt.data(), ntris, fast);
 	else fast.assign(1, DNode{});
+	std::vector<WNode> wide;
+	std::vector<DLeaf> wide_leaves;
+	build_wide_bvh8(fast, dt.data(), ntris, wide, wide_leaves);
 	CU(cudaStreamSynchronize(c->stream));
+	CU(c->wnodes.alloc(wide.size()));
+	CU(c->wleaves.alloc(std::max<size_t>(1, wide_leaves.size())));
+	CU(cudaMemcpyAsync(c->wnodes.p, wide.data(), sizeof(WNode) * wide.size(), cudaMemcpyHostToDevice, c->stream));
+	if (!wide_leaves.empty())
+		CU(cudaMemcpyAsync(c->wleaves.p, wide_leaves.data(), sizeof(DLeaf) * wide_leaves.size(), cudaMemcpyHostToDevice, c->stream));
 	CU(c->fast_nodes.alloc(fast.size()));
 	CU(cudaMemcpyAsync(c->fast_nodes.p, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
 	CU(c->nodes_ref.alloc(nnodes));
@@ -426,7 +444,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	c->force_reference = !contained;
 	c->cache_tris.assign(tris, tris + ntris);
 	c->cache_nodes.assign(nodes, nodes + nnodes);
-	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0};
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes.p, c->wnodes.p, c->wleaves.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags};
 	c->have_scene = true;
 	return MCPT_OK;
 }
@@ -472,7 +490,7 @@ int mcpt_intersect(mcpt_ctx* c, int traversal) {
 	// the live-ray counter (counters[2]) feeds stats.rays_traced for the stage path
 	const int trav = c->traversal(traversal);
 	const int g = blocks(c->npix, 128);
-	if (trav < 0 || trav > 2) return fail(MCPT_ERR_ARG, "unknown traversal");
+	if (trav < 0 || trav > 3) return fail(MCPT_ERR_ARG, "unknown traversal");
 	MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p)));
 	++c->launches;
 	CU(cudaGetLastError());
@@ -623,6 +641,7 @@ int mcpt_trace_count(mcpt_ctx* c, const mcpt_ray* d_rays, long n, int traversal)
 	if (!d_rays || n <= 0) return fail(MCPT_ERR_ARG, "mcpt_trace_count: bad arguments");
 	if (c->t_hits.n < size_t(n)) CU(c->t_hits.alloc(n));
 	CU(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * 3, c->stream));
+	CU(cudaMemsetAsync(c->counters.p + 5, 0, sizeof(unsigned long long), c->stream));
 	if (int r = launch_intersect(c, d_rays, n, c->t_hits.p, nullptr, traversal, true)) return r;
 	CU(cudaStreamSynchronize(c->stream));
 	return MCPT_OK;
@@ -676,6 +695,7 @@ int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
 	CU(cudaStreamSynchronize(c->stream));
 	out->nodes_fetched = h[0];
 	out->tris_fetched = h[1];
+	out->leaves_fetched = h[5];
 	out->rays_traced = h[2] + h[3];
 	out->paths = h[4] + c->stage_paths;
 	out->kernel_launches = c->launches;

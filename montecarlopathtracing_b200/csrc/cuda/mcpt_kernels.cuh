@@ -32,7 +32,8 @@ template <int TRAVERSAL, bool COUNT>
 __device__ __forceinline__ void trace_dispatch(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& h, unsigned long long* counters) {
 	if (TRAVERSAL == MCPT_TRAVERSAL_REFERENCE) trace_reference<COUNT>(sc, ray, tmin, h, counters, counters + 1);
 	else if (TRAVERSAL == MCPT_TRAVERSAL_CANONICAL) trace_canonical<COUNT>(sc, ray, tmin, h, counters, counters + 1);
-	else trace_fast<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+	else if (TRAVERSAL == MCPT_TRAVERSAL_WIDE8) trace_wide<COUNT>(sc, ray, tmin, h, counters, counters + 1);
+	else trace_ordered2<COUNT>(sc, ray, tmin, h, counters, counters + 1);
 }
 
 __device__ __forceinline__ RayRegs load_ray(const mcpt_ray* rays, long i) {
@@ -63,7 +64,7 @@ __global__ void k_fill_color(float4* color, int n, float v) {
 // ------------------------------------------------------------------ K2  (intersect.cl:1-28)
 // Writes the 48-byte Hit of the reference; `closest` (optional) gets the triangle whose data is in it.
 template <int TRAVERSAL, bool COUNT>
-__global__ void __launch_bounds__(128) k_intersect(SceneDev sc, const mcpt_ray* __restrict__ rays, long n, float tmin,
+__global__ void __launch_bounds__(256) k_intersect(SceneDev sc, const mcpt_ray* __restrict__ rays, long n, float tmin,
                                                     mcpt_hit* __restrict__ hits, int32_t* __restrict__ closest,
                                                     unsigned long long* counters) {
 	long i = long(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(256) k_wave_generate(CameraDev cam, WaveDev w,
 
 // One bounce for every live path: closest hit + shade + (terminate | compact into the next queue).
 template <int TRAVERSAL, bool COUNT>
-__global__ void __launch_bounds__(128) k_wave_bounce(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode,
+__global__ void __launch_bounds__(256) k_wave_bounce(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode,
                                                       unsigned long long* counters) {
 	const int src = depth & 1, dst = src ^ 1;
 	const uint32_t total = w.qcount[depth];

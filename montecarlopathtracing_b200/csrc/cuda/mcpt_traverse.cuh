@@ -29,12 +29,15 @@ struct SceneDev {
 	const mcpt_bvh_node* nodes_ref;
 	const mcpt_triangle* tris_ref;
 	const DNode* nodes;          // reference topology, two-box layout (canonical walk)
-	const DNode* fast_nodes;     // SAH tree over the same leaves (fast walk)
-	const DLeaf* leaves;
+	const DNode* fast_nodes;     // binary SAH tree over the same leaves (MCPT_TRAVERSAL_FAST)
+	const WNode* wnodes;         // 8-wide compressed collapse of that tree (MCPT_TRAVERSAL_WIDE8)
+	const DLeaf* wleaves;        // leaf records in wide-node order; DLeaf::pad = original triangle index
+	const DLeaf* leaves;         // leaf records indexed by triangle
 	const mcpt_material* materials;
 	const float2* cs_table;
 	int ntris, nnodes;
 	int root_is_leaf;
+	int opt_flags;               // development switches (MCPT_OPT): bit 0 = prefetch pushed nodes
 };
 
 struct HitRegs {
@@ -185,6 +188,110 @@ __device__ __forceinline__ void trace_canonical(const SceneDev& sc, const RayReg
 	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); }
 }
 
+// ------------------------------------------------------------------ certified-fast leaf tests
+// The reference's leaf decisions (six IEEE divisions for the box, nine for the triangle) are reproduced
+// WITHOUT divisions whenever the outcome is certain: the same quantities are evaluated with a reciprocal
+// multiply, an a-priori error bound is attached to each (|computed - reference's float value| <= bound),
+// and a comparison is taken only if it holds by more than the bound.  Anything closer than that - and any
+// NaN/Inf, which fails every "certain" test - is re-evaluated with the exact reference arithmetic
+// (intersect_aabb_exact / intersect_triangle).  Only the decisions and the final `t` enter the result, and
+// `t` of an accepted candidate is always computed with the reference's exact operations.
+//
+// Box: v~ = (bb - o) * RN(1/d) vs the reference's RN(RN(bb - o) / d): relative difference <= 3 * 2^-24;
+//      bound used 2^-21 |v~|.  accept <=> n_i <= f_j for all i != j and f_j >= tmin (same-axis n_i <= f_i holds
+//      identically in both evaluations, which also covers flat boxes where n_i == f_i).
+// Triangle: b~ = (A . num_b) * rcp(det) vs the reference's sum of RN(A_k * RN(num_k / det)): both are within
+//      a few 2^-24 of sum |A_k num_k / det| of the real value; bound used 2^-19 * sum |A_k num_k| |rcp(det)| + 1e-37.
+constexpr float BOX_REL = 4.76837158203125e-7f;       // 2^-21
+constexpr float TRI_REL = 1.9073486328125e-6f;        // 2^-19
+constexpr float TRI_ABS = 1e-37f;
+
+__device__ __forceinline__ float rcp_approx(float x) {
+	float r;
+	asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+	return r;
+}
+
+// 1 = box passes (and is not beyond tprune), 0 = rejected.  `fastok` is false for rays whose reciprocal
+// direction is not finite-safe (|d| < 1e-30): they always take the exact test.
+__device__ __forceinline__ bool leaf_box_certified(const float4& q0, const float4& q1, const RayRegs& ray, float rx, float ry,
+                                                   float rz, bool fastok, float tmin, float tprune) {
+	if (fastok) {
+		float l, h;
+		l = (q0.x - ray.origin.x) * rx; h = (q1.x - ray.origin.x) * rx;
+		const float nx = fminf(l, h), fx = fmaxf(l, h);
+		l = (q0.y - ray.origin.y) * ry; h = (q1.y - ray.origin.y) * ry;
+		const float ny = fminf(l, h), fy = fmaxf(l, h);
+		l = (q0.z - ray.origin.z) * rz; h = (q1.z - ray.origin.z) * rz;
+		const float nz = fminf(l, h), fz = fmaxf(l, h);
+		// upper bounds of the reference's n_i, lower bounds of its f_j
+		const float Nx = __fmaf_rn(BOX_REL, fabsf(nx), nx), Ny = __fmaf_rn(BOX_REL, fabsf(ny), ny), Nz = __fmaf_rn(BOX_REL, fabsf(nz), nz);
+		const float Fx = __fmaf_rn(-BOX_REL, fabsf(fx), fx), Fy = __fmaf_rn(-BOX_REL, fabsf(fy), fy), Fz = __fmaf_rn(-BOX_REL, fabsf(fz), fz);
+		const bool sure_accept = Nx <= Fy && Nx <= Fz && Ny <= Fx && Ny <= Fz && Nz <= Fx && Nz <= Fy && Fx >= tmin && Fy >= tmin && Fz >= tmin;
+		// lower bounds of n_i, upper bounds of f_j
+		const float Lx = __fmaf_rn(-BOX_REL, fabsf(nx), nx), Ly = __fmaf_rn(-BOX_REL, fabsf(ny), ny), Lz = __fmaf_rn(-BOX_REL, fabsf(nz), nz);
+		if (sure_accept) return !(fmaxf(fmaxf(Lx, Ly), Lz) > tprune);     // L <= true tnear: pruning stays safe
+		const float Ux = __fmaf_rn(BOX_REL, fabsf(fx), fx), Uy = __fmaf_rn(BOX_REL, fabsf(fy), fy), Uz = __fmaf_rn(BOX_REL, fabsf(fz), fz);
+		const bool sure_reject = Lx > Uy || Lx > Uz || Ly > Ux || Ly > Uz || Lz > Ux || Lz > Uy || Ux < tmin || Uy < tmin || Uz < tmin;
+		if (sure_reject) return false;
+	}
+	float tn;
+	if (!intersect_aabb_exact(q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, ray, tmin, tn)) return false;
+	return !(tn > tprune);
+}
+
+// Exact outcome of the reference triangle test for candidates that can matter: returns valid + the
+// reference's t.  Candidates certainly farther than `tfar_skip` (best + 2 * WINDOW) are reported invalid:
+// they can be neither near candidates nor band members.
+__device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restrict__ p, const RayRegs& ray, bool fastok, float tmin,
+                                                           float tfar_skip, int& orig_tri) {
+	const float4 q2 = __ldg(p + 2), q3 = __ldg(p + 3), q4 = __ldg(p + 4), q5 = __ldg(p + 5);
+	orig_tri = __float_as_int(q5.w);
+	TriTest out{0.0f, false};
+	const float a1 = ray.direction.x, a2 = ray.direction.y, a3 = ray.direction.z;
+	if (fabsf(q2.w * a1 + q3.w * a2 + q4.w * a3) < KERNEL_EPSILON) return out;      // objdef.h:186 (exact: no division)
+	const float e1x = q3.x, e1y = q3.y, e1z = q3.z, e2x = q4.x, e2y = q4.y, e2z = q4.z;
+	const float T2 = a2 * e2z - e2y * a3;
+	const float T3 = a2 * e1z - e1y * a3;
+	const float det = a1 * q5.x - e1x * T2 + e2x * T3;
+	if (fabsf(det) < KERNEL_EPSILON) return out;                                      // objdef.h:152 (exact)
+	const float Ax = q2.x - ray.origin.x, Ay = q2.y - ray.origin.y, Az = q2.z - ray.origin.z;
+	bool ambiguous = !fastok;
+	if (fastok) {
+		const float rd = rcp_approx(det), ard = fabsf(rd);
+		// b
+		float p1 = Ax * -T2, p2 = Ay * (a1 * e2z - e2x * a3), p3 = Az * -(a1 * e2y - e2x * a2);
+		const float bt = (p1 + p2 + p3) * rd;
+		const float bb = __fmaf_rn(TRI_REL, (fabsf(p1) + fabsf(p2) + fabsf(p3)) * ard, TRI_ABS);
+		if (bt < -bb) return out;
+		ambiguous |= !(bt > bb);
+		// c
+		p1 = Ax * T3; p2 = Ay * -(a1 * e1z - e1x * a3); p3 = Az * (a1 * e1y - e1x * a2);
+		const float ct = (p1 + p2 + p3) * rd;
+		const float cb = __fmaf_rn(TRI_REL, (fabsf(p1) + fabsf(p2) + fabsf(p3)) * ard, TRI_ABS);
+		if (ct < -cb) return out;
+		ambiguous |= !(ct > cb);
+		const float sum = bt + ct, sb = bb + cb + BOX_REL;
+		if (sum - 1.0f > sb) return out;
+		ambiguous |= !(1.0f - sum > sb);
+		// t
+		p1 = Ax * q5.x; p2 = Ay * -q5.y; p3 = Az * q5.z;
+		const float tt = (p1 + p2 + p3) * rd;
+		const float tb = __fmaf_rn(TRI_REL, (fabsf(p1) + fabsf(p2) + fabsf(p3)) * ard, TRI_ABS);
+		if (tt + tb < tmin) return out;              // reference t <= tmin for sure
+		if (tt - tb > tfar_skip) return out;         // certainly far: irrelevant to the near set
+	}
+	if (ambiguous)
+		return intersect_triangle(ray, q2.x, q2.y, q2.z, e1x, e1y, e1z, e2x, e2y, e2z, q5.x, q5.y, q5.z, q2.w, q3.w, q4.w, tmin);
+	// b, c and b + c certainly pass: the reference's t, with its exact operations (objdef.h:203-207)
+	const float s0 = q5.x / det, s4 = -q5.y / det, s8 = q5.z / det;
+	const float t = Ax * s0 + Ay * s4 + Az * s8;
+	if (t <= tmin) return out;
+	out.t = t;
+	out.valid = true;
+	return out;
+}
+
 // ------------------------------------------------------------------ ordered traversal + canonical replay
 //
 // trace_fast visits the tree NEAR CHILD FIRST and prunes against the closest candidate found so far, so
@@ -204,6 +311,9 @@ __device__ __forceinline__ void trace_canonical(const SceneDev& sc, const RayReg
 constexpr float WINDOW = 2.0e-5f;
 constexpr float BAND = 9.9e-6f;
 constexpr int LEAF_FLAG = int(0x80000000);
+#ifndef MCPT_POSTPONE_LEAF
+#define MCPT_POSTPONE_LEAF 1
+#endif
 
 struct CandList {
 	float t0, t1, t2;
@@ -255,13 +365,14 @@ __device__ __forceinline__ bool cand_resolve(const CandList& c, float best, HitR
 }
 
 template <bool COUNT>
-__device__ __forceinline__ void trace_fast(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
-                                           unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
+__device__ __forceinline__ void trace_ordered2(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
+                                               unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
 	if (ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf) {
 		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 		return;
 	}
 	const float rx = 1.0f / ray.direction.x, ry = 1.0f / ray.direction.y, rz = 1.0f / ray.direction.z;
+	const bool fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
 	int stack[STACK_SIZE];     // >= 0 inner node; LEAF_FLAG | triangle for a leaf
 	int sp = 0;
 	int cur = 0;
@@ -270,9 +381,10 @@ __device__ __forceinline__ void trace_fast(const SceneDev& sc, const RayRegs& ra
 	cl.n = 0; cl.overflow = false;
 	cl.t0 = cl.t1 = cl.t2 = 0.f; cl.tri0 = cl.tri1 = cl.tri2 = 0; cl.rank0 = cl.rank1 = cl.rank2 = 0;
 	bool any = false;
-	unsigned ln = 0, lt = 0;
+	unsigned ln = 0, lt = 0, lr = 0;
 	const int DONE = 0x7fffffff;
-	while (cur != DONE) {
+	int pending = 0;           // postponed leaf (0 = none; leaf codes carry LEAF_FLAG, so they are never 0)
+	while (cur != DONE || pending != 0) {
 		// ---- inner nodes: conservative tests of both children, near child first
 		while (cur >= 0 && cur != DONE) {
 			const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
@@ -304,31 +416,163 @@ __device__ __forceinline__ void trace_fast(const SceneDev& sc, const RayRegs& ra
 				const bool swap = loR < loL;
 				const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
 				if (sp < STACK_SIZE) stack[sp++] = farc; else cl.overflow = true;
+				if (sc.opt_flags & 1) {
+					const void* pf = farc >= 0 ? (const void*)(sc.fast_nodes + farc) : (const void*)(sc.leaves + (farc & 0x7fffffff));
+					asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
+				}
 				cur = nearc;
 			} else if (hitL) cur = cl_;
 			else if (hitR) cur = cr_;
 			else cur = sp > 0 ? stack[--sp] : DONE;
+#if MCPT_POSTPONE_LEAF
+			// the first leaf found is postponed so that the lane keeps traversing while its warp mates still
+			// search: candidates need not arrive in any particular order (see the replay argument above)
+			if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? stack[--sp] : DONE; }
+#endif
 		}
-		// ---- leaf: exact reference box test, then the exact triangle test
-		if (cur != DONE) {
-			const int tri = cur & 0x7fffffff;
+		// ---- leaves: exact reference box test, then the exact triangle test
+		while (pending != 0 || cur < 0) {
+			int leaf;
+			if (pending != 0) { leaf = pending; pending = 0; }
+			else { leaf = cur; cur = sp > 0 ? stack[--sp] : DONE; }
+			const int tri = leaf & 0x7fffffff;
 			const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
-			float4 q0 = __ldg(p), q1 = __ldg(p + 1);
-			if (COUNT) ++ln;
-			float tn;
-			if (intersect_aabb_exact(q0.x, q0.y, q0.z, q1.x, q1.y, q1.z, ray, tmin, tn) && !(tn > best * PRUNE_REL + PRUNE_ABS)) {
+			const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
+			if (COUNT) ++lr;
+			if (leaf_box_certified(q0, q1, ray, rx, ry, rz, fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
 				if (COUNT) ++lt;
-				TriTest r = leaf_triangle(sc.leaves, tri, ray, tmin);
+				int orig;
+				TriTest r = leaf_triangle_certified(p, ray, fastok, tmin, best + 2.0f * WINDOW, orig);
 				if (r.valid) {
 					any = true;
 					if (r.t < best) best = r.t;
-					if (!(r.t - best > WINDOW)) cand_insert(cl, best, r.t, tri, __float_as_int(q0.w));
+					if (!(r.t - best > WINDOW)) cand_insert(cl, best, r.t, orig, __float_as_int(q0.w));
 				}
 			}
-			cur = sp > 0 ? stack[--sp] : DONE;
 		}
 	}
-	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); }
+	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); atomicAdd(cnt_nodes + 5, (unsigned long long)lr); }
+	hit.any = any;
+	if (cl.overflow || !cand_resolve(cl, best, hit)) {
+		hit = HitRegs{FLT_MAX, -1, 0, false};
+		trace_canonical<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
+	}
+}
+
+// ------------------------------------------------------------------ 8-wide compressed traversal (experimental)
+// Same candidate / replay logic as trace_ordered2; inner tests run on 8-bit quantised child boxes that
+// contain the true child boxes (outward rounding, verified in exact arithmetic at build time).  Plane
+// distances are one FFMA each: t = q * (scale/d) + (p - o)/d.  With A = (p-o)*r, B = scale*r the computed
+// value is within 2^-22 (|A| + 255 |B|) of the exact distance to the quantised plane; every near plane is
+// moved down and every far plane up by s = 2^-20 (|A| + 256 |B|) PER AXIS (a per-axis slack cannot blow
+// up the way a per-ray |o/d| term would: an axis the ray is parallel to has huge planes AND a huge slack,
+// but they only matter when the origin is within 1e-6 of that slab's boundary).
+constexpr int WSTACK = 32;
+
+template <bool COUNT>
+__device__ __forceinline__ void trace_wide(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
+                                           unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
+	if (ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf) {
+		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
+		return;
+	}
+	// 2^23 * scale / d must stay finite for the byte -> float trick below: steeper rays use the binary walk
+	if (!(fabsf(ray.direction.x) > 1e-20f && fabsf(ray.direction.y) > 1e-20f && fabsf(ray.direction.z) > 1e-20f)) {
+		trace_ordered2<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
+		return;
+	}
+	const float rx = 1.0f / ray.direction.x, ry = 1.0f / ray.direction.y, rz = 1.0f / ray.direction.z;
+	const bool fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
+	const bool posx = ray.direction.x >= 0.0f, posy = ray.direction.y >= 0.0f, posz = ray.direction.z >= 0.0f;
+	const unsigned octinv = (posx ? 1u : 0u) | (posy ? 2u : 0u) | (posz ? 4u : 0u);
+	uint2 stack[WSTACK];
+	int sp = 0;
+	uint2 ng = make_uint2(0u, 0x80000000u);       // virtual group holding the root (imask 0 => relative index 0)
+	float best = FLT_MAX;
+	CandList cl;
+	cl.n = 0; cl.overflow = false;
+	cl.t0 = cl.t1 = cl.t2 = 0.f; cl.tri0 = cl.tri1 = cl.tri2 = 0; cl.rank0 = cl.rank1 = cl.rank2 = 0;
+	bool any = false;
+	unsigned ln = 0, lt = 0, lr = 0;
+	for (;;) {
+		uint2 tg = make_uint2(0u, 0u);
+		if (ng.y > 0x00FFFFFFu) {
+			// ---- next inner child of the current group (highest bit first = nearest octant first)
+			const unsigned bit = 31u - unsigned(__clz(int(ng.y)));
+			const unsigned gmask = ng.y & 0xFFu;
+			ng.y &= ~(1u << bit);
+			if (ng.y > 0x00FFFFFFu) { if (sp < WSTACK) stack[sp++] = ng; else cl.overflow = true; }
+			const unsigned slot = (bit - 24u) ^ octinv;
+			const unsigned rel = unsigned(__popc(gmask & ((1u << slot) - 1u)));
+			const float4* p = reinterpret_cast<const float4*>(sc.wnodes + (ng.x + rel));
+			const float4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
+			if (COUNT) ++ln;
+			const unsigned ew = __float_as_uint(n0.w);
+			const float sx = __uint_as_float((ew & 0xFFu) << 23), sy = __uint_as_float(((ew >> 8) & 0xFFu) << 23),
+			            sz = __uint_as_float(((ew >> 16) & 0xFFu) << 23);
+			const float Bx = sx * rx, By = sy * ry, Bz = sz * rz;
+			const float Ax = (n0.x - ray.origin.x) * rx, Ay = (n0.y - ray.origin.y) * ry, Az = (n0.z - ray.origin.z) * rz;
+			// A byte q becomes the float 2^23 + q with ONE permute (0x4B0000qq); the 2^23 * B is folded into the
+			// constant term, whose rounding costs at most half a quantisation step |B|/2 -> one extra |B| of slack.
+			const float slx = SLAB_SLACK * (fabsf(Ax) + 256.0f * fabsf(Bx)) + fabsf(Bx), sly = SLAB_SLACK * (fabsf(Ay) + 256.0f * fabsf(By)) + fabsf(By),
+			            slz = SLAB_SLACK * (fabsf(Az) + 256.0f * fabsf(Bz)) + fabsf(Bz);
+			const float Mx = Ax - 8388608.0f * Bx, My = Ay - 8388608.0f * By, Mz = Az - 8388608.0f * Bz;
+			const float Anx = Mx - slx, Afx = Mx + slx, Any = My - sly, Afy = My + sly, Anz = Mz - slz, Afz = Mz + slz;
+			// near / far quantised planes per axis, chosen by the ray octant
+			const unsigned qlx0 = __float_as_uint(n2.x), qlx1 = __float_as_uint(n2.y), qly0 = __float_as_uint(n2.z), qly1 = __float_as_uint(n2.w);
+			const unsigned qlz0 = __float_as_uint(n3.x), qlz1 = __float_as_uint(n3.y), qhx0 = __float_as_uint(n3.z), qhx1 = __float_as_uint(n3.w);
+			const unsigned qhy0 = __float_as_uint(n4.x), qhy1 = __float_as_uint(n4.y), qhz0 = __float_as_uint(n4.z), qhz1 = __float_as_uint(n4.w);
+			const unsigned nx[2] = {posx ? qlx0 : qhx0, posx ? qlx1 : qhx1}, fx[2] = {posx ? qhx0 : qlx0, posx ? qhx1 : qlx1};
+			const unsigned ny[2] = {posy ? qly0 : qhy0, posy ? qly1 : qhy1}, fy[2] = {posy ? qhy0 : qly0, posy ? qhy1 : qly1};
+			const unsigned nz[2] = {posz ? qlz0 : qhz0, posz ? qlz1 : qhz1}, fz[2] = {posz ? qhz0 : qlz0, posz ? qhz1 : qlz1};
+			const unsigned meta[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
+			const float tprune = best * PRUNE_REL + PRUNE_ABS;
+			unsigned hitmask = 0u;
+#pragma unroll
+			for (int c = 0; c < 8; ++c) {
+				const int w = c >> 2, sh = (c & 3) * 8;
+				const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nx[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bx, Anx);
+				const float tny = __fmaf_rn(__uint_as_float(__byte_perm(ny[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), By, Any);
+				const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nz[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bz, Anz);
+				const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(fx[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bx, Afx);
+				const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fy[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), By, Afy);
+				const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(fz[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bz, Afz);
+				const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
+				const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tprune));
+				const unsigned m = (meta[w] >> sh) & 0xFFu;
+				if (!(tn > tf)) {                           // false on NaN => kept (conservative)
+					unsigned idx = m & 31u;
+					if (idx >= 24u) idx ^= octinv;
+					hitmask |= (m >> 5) << idx;
+				}
+			}
+			ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xFF000000u) | (ew >> 24));
+			tg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
+		}
+		// ---- leaf records of this node: exact reference box test, then the exact triangle test
+		while (tg.y != 0u) {
+			const unsigned bit = unsigned(__ffs(int(tg.y))) - 1u;
+			tg.y &= tg.y - 1u;
+			const float4* p = reinterpret_cast<const float4*>(sc.wleaves + (tg.x + bit));
+			const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
+			if (COUNT) ++lr;
+			if (leaf_box_certified(q0, q1, ray, rx, ry, rz, fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
+				if (COUNT) ++lt;
+				int orig;
+				TriTest r = leaf_triangle_certified(p, ray, fastok, tmin, best + 2.0f * WINDOW, orig);
+				if (r.valid) {
+					any = true;
+					if (r.t < best) best = r.t;
+					if (!(r.t - best > WINDOW)) cand_insert(cl, best, r.t, orig, __float_as_int(q0.w));
+				}
+			}
+		}
+		if (ng.y <= 0x00FFFFFFu) {
+			if (sp == 0) break;
+			ng = stack[--sp];
+		}
+	}
+	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); atomicAdd(cnt_nodes + 5, (unsigned long long)lr); }
 	hit.any = any;
 	if (cl.overflow || !cand_resolve(cl, best, hit)) {
 		hit = HitRegs{FLT_MAX, -1, 0, false};

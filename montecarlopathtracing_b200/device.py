@@ -16,7 +16,7 @@ from . import types as T
 _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
-TRAVERSAL_REFERENCE, TRAVERSAL_FAST, TRAVERSAL_CANONICAL = 0, 1, 2
+TRAVERSAL_REFERENCE, TRAVERSAL_FAST, TRAVERSAL_CANONICAL, TRAVERSAL_WIDE8 = 0, 1, 2, 3
 
 EXPORTS = [
     "mcpt_last_error", "mcpt_abi_version", "mcpt_create", "mcpt_destroy", "mcpt_stream", "mcpt_synchronize",
@@ -38,7 +38,8 @@ class Params(ctypes.Structure):
 
 class Stats(ctypes.Structure):
     _fields_ = [("rays_traced", ctypes.c_uint64), ("paths", ctypes.c_uint64), ("kernel_launches", ctypes.c_uint64),
-                ("nodes_fetched", ctypes.c_uint64), ("tris_fetched", ctypes.c_uint64)]
+                ("nodes_fetched", ctypes.c_uint64), ("tris_fetched", ctypes.c_uint64),
+                ("leaves_fetched", ctypes.c_uint64)]
 
 
 def library_path():

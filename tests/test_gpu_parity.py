@@ -9,7 +9,7 @@ from tests.util import adversarial_rays, hit_mismatches, hits_equal, random_rays
 
 pytestmark = pytest.mark.gpu
 
-ALL_TRAVERSALS = [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST, device.TRAVERSAL_CANONICAL]
+ALL_TRAVERSALS = [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST, device.TRAVERSAL_CANONICAL, device.TRAVERSAL_WIDE8]
 SCENE_RES = {"cbox": (256, 256), "mis": (320, 180)}
 
 
@@ -85,6 +85,9 @@ def test_trace_edge_cases(cbox):
         rays["direction"][::7, 0] = 0.0                          # zero components: Inf/NaN slab arithmetic
         rays["direction"][::11, 1] = 0.0
         rays["direction"][::13] = (0.0, 0.0, 1.0)
+        rays["direction"][1::17, 0] = 1e-33                    # reciprocal overflows to inf: certified tests must defer
+        rays["direction"][2::19, 2] = -3e-39                   # denormal component
+        rays["direction"][3::23, 1] = 1e-12                    # huge but finite reciprocal
         rays["state"][::5] = np.int32(-16777216)                 # terminated rays: hit record left untouched
         ref_hits, ref_closest = O.intersect(rays, cbox.nodes, cbox.triangles)
         for trav in ALL_TRAVERSALS:
