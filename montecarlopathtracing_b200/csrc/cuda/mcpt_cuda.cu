@@ -76,7 +76,8 @@ struct mcpt_ctx {
 	// wavefront path
 	int wave_samples = 0;             // allocated samples per wave
 	DevBuf<float4> od[2], dp[2], cs[2], sample_out;
-	DevBuf<uint32_t> qcount, first_sample;
+	DevBuf<uint32_t> qcount, qhead, first_sample;   // qhead[d]: work-fetch cursor of the persistent bounce d (+1 slot for mcpt_trace)
+	int nsm = 148;
 	DevBuf<unsigned long long> counters;   // 0 nodes, 1 tris, 2 live rays (stage path), 3 rays (wave), 4 paths (wave)
 	// trace scratch
 	DevBuf<mcpt_ray> t_rays;
@@ -129,6 +130,7 @@ struct mcpt_ctx {
 		return w;
 	}
 	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
+	int persistent_grid(int bs) const { return nsm * (MCPT_MIN_BLOCKS * 128 / bs); }
 };
 
 // expands `stmt` with TRAV bound to the compile-time traversal id
@@ -184,6 +186,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	const long total = long(nsamples) * c->npix;
 	WaveDev w = c->wave();
 	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	CU(cudaMemsetAsync(c->qhead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int trav = c->traversal(c->prm.traversal);
 	const int BS = c->block;
@@ -207,6 +210,8 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 		}
 		if (c->count_fetches)
 			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, true><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
+		else if (trav == MCPT_TRAVERSAL_FAST && !(c->opt_flags & 2))
+			k_wave_bounce_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, c->qhead.p + d);
 		else
 			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, false><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
 		if (c->time_bounces) {
@@ -228,7 +233,11 @@ int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hi
 	if (trav < 0 || trav > 3) return fail(MCPT_ERR_ARG, "unknown traversal");
 	if (count)
 		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, BS, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
-	else
+	else if (trav == MCPT_TRAVERSAL_FAST && !(c->opt_flags & 2) && n < (1L << 32)) {
+		unsigned* head = c->qhead.p + c->prm.max_depth + 1;
+		CU(cudaMemsetAsync(head, 0, sizeof(unsigned), c->stream));
+		k_intersect_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, d_rays, unsigned(n), c->prm.tmin, d_hits, d_closest, head);
+	} else
 		MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, false><<<g, BS, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, cnt)));
 	++c->launches;
 	CU(cudaGetLastError());
@@ -270,14 +279,15 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	if (c->prm.tmin == 0.0f) c->prm.tmin = 0.001f;
 	if (c->prm.seed_mode == 0) c->prm.samples_in_flight = 1;
 	c->npix = params->width * params->height;
+	c->nsm = prop.multiProcessorCount;
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
-	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128 || b == 256) c->block = b; }
+	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128) c->block = b; }
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
 	ok = ok && c->rays.alloc(n) == cudaSuccess && c->hits.alloc(n) == cudaSuccess && c->closest.alloc(n) == cudaSuccess &&
 	     c->color.alloc(n) == cudaSuccess && c->hist.alloc(n) == cudaSuccess && c->display.alloc(n) == cudaSuccess &&
 	     c->seeds.alloc(n) == cudaSuccess && c->counts.alloc(n) == cudaSuccess && c->sums_own.alloc(7 * n) == cudaSuccess &&
-	     c->qcount.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->first_sample.alloc(1) == cudaSuccess &&
+	     c->qcount.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->qhead.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->first_sample.alloc(1) == cudaSuccess &&
 	     c->counters.alloc(8) == cudaSuccess;
 	if (ok) {
 		c->sums = c->sums_own.p;

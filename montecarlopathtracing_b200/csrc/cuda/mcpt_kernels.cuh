@@ -273,3 +273,169 @@ __global__ void k_init_seeds(uint32_t* seeds, int n, uint32_t run_seed) {
 }
 
 }  // namespace mcpt
+
+// ================================================================== persistent kernels (MCPT_TRAVERSAL_FAST)
+// Rays of very different traversal length share a warp; with one thread per ray the warp runs until its
+// longest ray is done (measured: 13 of 32 lanes active in the inner loop on incoherent rays).  Here each
+// warp keeps pulling work: whenever fewer than REFILL_THRESHOLD lanes are still walking, the idle lanes
+// first FINISH their completed rays together (hit record / shading / queue compaction - also the divergent
+// part, so batching it matters) and then fetch new work items with one atomic per warp.
+namespace mcpt {
+
+#ifndef MCPT_MIN_BLOCKS
+#define MCPT_MIN_BLOCKS 8        // resident 128-thread blocks per SM the persistent kernels are compiled for (8 -> 64 registers)
+#endif
+#ifndef MCPT_REFILL_THRESHOLD
+#define MCPT_REFILL_THRESHOLD 22
+#endif
+
+// Job: bool load(unsigned item, RayRegs&) - false when the item needs no trace (the job has dealt with it);
+//      void finish(unsigned item, const RayRegs&, const HitRegs&)
+template <class Job>
+__device__ __forceinline__ void persistent_walk(const SceneDev& sc, float tmin, unsigned total, unsigned* head, Job& job) {
+	const unsigned FULL = 0xffffffffu;
+	const unsigned lane = threadIdx.x & 31u;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	Walk2 w;
+	RayRegs ray;
+	unsigned item = 0;
+	bool working = false, have_result = false, exhausted = false;
+	for (;;) {
+		unsigned wm = __ballot_sync(FULL, working);
+		if (__popc(wm) < MCPT_REFILL_THRESHOLD) {
+			if (have_result) {
+				HitRegs h;
+				walk2_resolve<false>(w, sc, ray, tmin, h, nullptr, nullptr);
+				job.finish(item, ray, h);
+				have_result = false;
+			}
+			if (!exhausted) {
+				bool want = !working;
+				unsigned m = __ballot_sync(FULL, want);
+				while (m) {                                    // warp-uniform loop
+					const unsigned n = unsigned(__popc(m));
+					unsigned base = 0;
+					if (lane == unsigned(__ffs(int(m))) - 1u) base = atomicAdd(head, n);
+					base = __shfl_sync(FULL, base, __ffs(int(m)) - 1);
+					if (want) {
+						const unsigned i = base + unsigned(__popc(m & lt_mask));
+						if (i < total) {
+							item = i;
+							if (job.load(i, ray)) {
+								walk2_init(w, sc, ray);
+								working = true;
+								want = false;
+							}
+						} else {
+							want = false;
+						}
+					}
+					if (base + n >= total) exhausted = true;   // base, n are warp-uniform
+					m = exhausted ? 0u : __ballot_sync(FULL, want);
+				}
+			}
+			wm = __ballot_sync(FULL, working);
+			if (wm == 0u) break;
+		}
+		if (working) {
+			walk2_round<false>(w, sc, ray, tmin);
+			if (walk2_finished(w)) { working = false; have_result = true; }
+		}
+	}
+}
+
+struct IntersectJob {
+	const SceneDev& sc;
+	const mcpt_ray* rays;
+	mcpt_hit* hits;
+	int32_t* closest;
+	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+		ray = load_ray(rays, long(i));
+		if (uint32_t(__float_as_int(ray.origin.w)) & MCPT_RAY_TERM_MASK) {      // intersect.cl:16
+			if (closest) closest[i] = -1;
+			return false;
+		}
+		return true;
+	}
+	__device__ __forceinline__ void finish(unsigned i, const RayRegs& ray, const HitRegs& h) {
+		float4 nrm = make_float4(0, 0, 0, 0), pt = make_float4(0, 0, 0, 0);
+		uint32_t mat = 0;
+		if (h.closest >= 0) {
+			const float4* tp = reinterpret_cast<const float4*>(sc.leaves + h.closest);
+			float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+			f4 nn{q2.w, q3.w, q4.w, 0.0f};
+			mat = uint32_t(__float_as_int(q1.w));
+			pt = st4(ray.origin + h.t * ray.direction);
+			if (h.any && dot3(ray.direction, nn) > 0) nn = -nn;
+			nrm = st4(nn);
+		}
+		float4* hp = reinterpret_cast<float4*>(hits + i);
+		hp[0] = nrm;
+		hp[1] = pt;
+		hp[2] = make_float4(h.t, __int_as_float(h.closest >= 0 ? h.closest : 0), __int_as_float(int(mat)), __int_as_float(0));
+		if (closest) closest[i] = h.closest;
+	}
+};
+
+__global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_intersect_persistent(SceneDev sc, const mcpt_ray* __restrict__ rays, unsigned n, float tmin,
+                                                              mcpt_hit* __restrict__ hits, int32_t* __restrict__ closest, unsigned* head) {
+	IntersectJob job{sc, rays, hits, closest};
+	persistent_walk(sc, tmin, n, head, job);
+}
+
+struct BounceJob {
+	const SceneDev& sc;
+	const WaveDev& w;
+	int depth, max_depth, seed_mode, src, dst;
+	// per-lane path state carried from load to finish
+	f4 color;
+	uint32_t seed;
+	int path;
+	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+		float4 o = w.od[src][i], d = w.dp[src][i], c = w.cs[src][i];
+		path = __float_as_int(d.w);
+		ray.origin = ld4(o);
+		ray.direction = f4{d.x, d.y, d.z, __int_as_float(path % w.npix)};
+		color = f4{c.x, c.y, c.z, 0.0f};
+		seed = uint32_t(__float_as_int(c.w));
+		return true;
+	}
+	__device__ __forceinline__ void finish(unsigned, RayRegs ray, const HitRegs& h) {
+		f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
+		uint32_t mat = 0;
+		if (h.closest >= 0) {
+			const float4* tp = reinterpret_cast<const float4*>(sc.leaves + h.closest);
+			float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+			nn = f4{q2.w, q3.w, q4.w, 0.0f};
+			mat = uint32_t(__float_as_int(q1.w));
+			ip = ray.origin + h.t * ray.direction;
+			if (dot3(ray.direction, nn) > 0) nn = -nn;
+		}
+		const bool alive = shade_one(sc.materials, sc.cs_table, ray, h.t, nn, ip, mat, color, seed, max_depth);
+		if (!alive) {
+			w.sample_out[path] = make_float4(color.x, color.y, color.z, 0.0f);
+			if (seed_mode == 0) w.seeds[path % w.npix] = seed;
+		} else {
+			// queue compaction among the lanes that reach this point together: one atomic per group
+			const unsigned m = __activemask();
+			const unsigned lane = threadIdx.x & 31u;
+			const int leader = __ffs(int(m)) - 1;
+			uint32_t base = 0;
+			if (int(lane) == leader) base = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(m)));
+			base = __shfl_sync(m, base, leader);
+			const uint32_t pos = base + uint32_t(__popc(m & ((1u << lane) - 1u)));
+			w.od[dst][pos] = st4(ray.origin);
+			w.dp[dst][pos] = make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path));
+			w.cs[dst][pos] = make_float4(color.x, color.y, color.z, __int_as_float(int(seed)));
+		}
+	}
+};
+
+__global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_bounce_persistent(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode,
+                                                                unsigned* head) {
+	const unsigned total = w.qcount[depth];
+	BounceJob job{sc, w, depth, max_depth, seed_mode, depth & 1, (depth & 1) ^ 1, f4{0, 0, 0, 0}, 0u, 0};
+	persistent_walk(sc, tmin, total, head, job);
+}
+
+}  // namespace mcpt

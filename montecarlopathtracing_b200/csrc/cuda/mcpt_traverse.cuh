@@ -37,7 +37,7 @@ struct SceneDev {
 	const float2* cs_table;
 	int ntris, nnodes;
 	int root_is_leaf;
-	int opt_flags;               // development switches (MCPT_OPT): bit 0 = prefetch pushed nodes
+	int opt_flags;               // development switches (MCPT_OPT): bit 1 = one-thread-per-ray kernels instead of persistent ones
 };
 
 struct HitRegs {
@@ -364,99 +364,126 @@ __device__ __forceinline__ bool cand_resolve(const CandList& c, float best, HitR
 	return ok;
 }
 
-template <bool COUNT>
-__device__ __forceinline__ void trace_ordered2(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
-                                               unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
-	if (ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf) {
-		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
-		return;
-	}
-	const float rx = 1.0f / ray.direction.x, ry = 1.0f / ray.direction.y, rz = 1.0f / ray.direction.z;
-	const bool fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
+// State of one ordered binary walk, so that the persistent kernels can advance many rays round by round
+// (a "round" = descend inner nodes until a leaf turns up, then test the leaves at hand).
+struct Walk2 {
 	int stack[STACK_SIZE];     // >= 0 inner node; LEAF_FLAG | triangle for a leaf
-	int sp = 0;
-	int cur = 0;
-	float best = FLT_MAX;
+	int sp, cur, pending;      // pending: postponed leaf (0 = none; leaf codes carry LEAF_FLAG, so they are never 0)
+	float best;
+	float rx, ry, rz;
 	CandList cl;
-	cl.n = 0; cl.overflow = false;
-	cl.t0 = cl.t1 = cl.t2 = 0.f; cl.tri0 = cl.tri1 = cl.tri2 = 0; cl.rank0 = cl.rank1 = cl.rank2 = 0;
-	bool any = false;
-	unsigned ln = 0, lt = 0, lr = 0;
-	const int DONE = 0x7fffffff;
-	int pending = 0;           // postponed leaf (0 = none; leaf codes carry LEAF_FLAG, so they are never 0)
-	while (cur != DONE || pending != 0) {
-		// ---- inner nodes: conservative tests of both children, near child first
-		while (cur >= 0 && cur != DONE) {
-			const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
-			float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-			int4 link = __ldg(reinterpret_cast<const int4*>(p + 3));
-			if (COUNT) ++ln;
-			const float tprune = best * PRUNE_REL + PRUNE_ABS;
-			// (bb - o) * (1/d): |computed - reference| <= 2^-22 |t|, covered 4x by the 2^-20 relative slack.  (A single
-			// fused bb*(1/d) - o*(1/d) is cheaper but its error scales with |o/d|: rays nearly parallel to an axis
-			// would then accept every box - measured 3x slower on random rays, so it is not used.)
-			float o1, o2, n0, n1, n2, f0, f1, f2;
-			o1 = (a.x - ray.origin.x) * rx; o2 = (a.w - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
-			o1 = (a.y - ray.origin.y) * ry; o2 = (b.x - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
-			o1 = (a.z - ray.origin.z) * rz; o2 = (b.y - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
-			float tnL = fmaxf(fmaxf(n0, n1), n2), tfL = fminf(fminf(f0, f1), f2);
-			o1 = (b.z - ray.origin.x) * rx; o2 = (c.y - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
-			o1 = (b.w - ray.origin.y) * ry; o2 = (c.z - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
-			o1 = (c.x - ray.origin.z) * rz; o2 = (c.w - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
-			float tnR = fmaxf(fmaxf(n0, n1), n2), tfR = fminf(fminf(f0, f1), f2);
-			const float sL = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnL), fabsf(tfL)), tmin);
-			const float sR = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnR), fabsf(tfR)), tmin);
-			const float loL = tnL - sL, loR = tnR - sR;
-			// comparisons are false on NaN => not rejected (conservative)
-			const bool hitL = !((tfL < loL) || (tfL < tmin - sL) || (loL > tprune));
-			const bool hitR = !((tfR < loR) || (tfR < tmin - sR) || (loR > tprune));
-			int cl_ = link.x < 0 ? (LEAF_FLAG | ~link.x) : link.x;
-			int cr_ = link.y < 0 ? (LEAF_FLAG | ~link.y) : link.y;
-			if (hitL && hitR) {
-				const bool swap = loR < loL;
-				const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
-				if (sp < STACK_SIZE) stack[sp++] = farc; else cl.overflow = true;
-				if (sc.opt_flags & 1) {
-					const void* pf = farc >= 0 ? (const void*)(sc.fast_nodes + farc) : (const void*)(sc.leaves + (farc & 0x7fffffff));
-					asm volatile("prefetch.global.L1 [%0];" ::"l"(pf));
-				}
-				cur = nearc;
-			} else if (hitL) cur = cl_;
-			else if (hitR) cur = cr_;
-			else cur = sp > 0 ? stack[--sp] : DONE;
+	bool fastok, slow;         // slow: zero direction component or single-triangle scene -> reference walk
+	unsigned ln, lt, lr;       // instrumentation
+};
+constexpr int WALK_DONE = 0x7fffffff;
+
+__device__ __forceinline__ void walk2_init(Walk2& w, const SceneDev& sc, const RayRegs& ray) {
+	w.slow = ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf;
+	w.rx = 1.0f / ray.direction.x; w.ry = 1.0f / ray.direction.y; w.rz = 1.0f / ray.direction.z;
+	w.fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
+	w.sp = 0;
+	w.cur = w.slow ? WALK_DONE : 0;
+	w.pending = 0;
+	w.best = FLT_MAX;
+	w.cl.n = 0; w.cl.overflow = false;
+	w.cl.t0 = w.cl.t1 = w.cl.t2 = 0.f; w.cl.tri0 = w.cl.tri1 = w.cl.tri2 = 0; w.cl.rank0 = w.cl.rank1 = w.cl.rank2 = 0;
+	w.ln = w.lt = w.lr = 0;
+}
+
+__device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur == WALK_DONE && w.pending == 0; }
+
+template <bool COUNT>
+__device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const RayRegs& ray, float tmin) {
+	const float rx = w.rx, ry = w.ry, rz = w.rz;
+	int cur = w.cur, sp = w.sp, pending = w.pending;
+	float best = w.best;
+	// ---- inner nodes: conservative tests of both children, near child first
+	while (cur >= 0 && cur != WALK_DONE) {
+		const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
+		float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+		int4 link = __ldg(reinterpret_cast<const int4*>(p + 3));
+		if (COUNT) ++w.ln;
+		const float tprune = best * PRUNE_REL + PRUNE_ABS;
+		// (bb - o) * (1/d): |computed - reference| <= 2^-22 |t|, covered 4x by the 2^-20 relative slack.  (A single
+		// fused bb*(1/d) - o*(1/d) is cheaper but its error scales with |o/d|: rays nearly parallel to an axis
+		// would then accept every box - measured 3x slower on random rays, so it is not used.)
+		float o1, o2, n0, n1, n2, f0, f1, f2;
+		o1 = (a.x - ray.origin.x) * rx; o2 = (a.w - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
+		o1 = (a.y - ray.origin.y) * ry; o2 = (b.x - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
+		o1 = (a.z - ray.origin.z) * rz; o2 = (b.y - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
+		float tnL = fmaxf(fmaxf(n0, n1), n2), tfL = fminf(fminf(f0, f1), f2);
+		o1 = (b.z - ray.origin.x) * rx; o2 = (c.y - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
+		o1 = (b.w - ray.origin.y) * ry; o2 = (c.z - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
+		o1 = (c.x - ray.origin.z) * rz; o2 = (c.w - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
+		float tnR = fmaxf(fmaxf(n0, n1), n2), tfR = fminf(fminf(f0, f1), f2);
+		const float sL = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnL), fabsf(tfL)), tmin);
+		const float sR = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnR), fabsf(tfR)), tmin);
+		const float loL = tnL - sL, loR = tnR - sR;
+		// comparisons are false on NaN => not rejected (conservative)
+		const bool hitL = !((tfL < loL) || (tfL < tmin - sL) || (loL > tprune));
+		const bool hitR = !((tfR < loR) || (tfR < tmin - sR) || (loR > tprune));
+		int cl_ = link.x < 0 ? (LEAF_FLAG | ~link.x) : link.x;
+		int cr_ = link.y < 0 ? (LEAF_FLAG | ~link.y) : link.y;
+		if (hitL && hitR) {
+			const bool swap = loR < loL;
+			const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
+			if (sp < STACK_SIZE) w.stack[sp++] = farc; else w.cl.overflow = true;
+			cur = nearc;
+		} else if (hitL) cur = cl_;
+		else if (hitR) cur = cr_;
+		else cur = sp > 0 ? w.stack[--sp] : WALK_DONE;
 #if MCPT_POSTPONE_LEAF
-			// the first leaf found is postponed so that the lane keeps traversing while its warp mates still
-			// search: candidates need not arrive in any particular order (see the replay argument above)
-			if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? stack[--sp] : DONE; }
+		// the first leaf found is postponed so that the lane keeps traversing while its warp mates still
+		// search: candidates need not arrive in any particular order (see the replay argument above)
+		if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? w.stack[--sp] : WALK_DONE; }
 #endif
-		}
-		// ---- leaves: exact reference box test, then the exact triangle test
-		while (pending != 0 || cur < 0) {
-			int leaf;
-			if (pending != 0) { leaf = pending; pending = 0; }
-			else { leaf = cur; cur = sp > 0 ? stack[--sp] : DONE; }
-			const int tri = leaf & 0x7fffffff;
-			const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
-			const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
-			if (COUNT) ++lr;
-			if (leaf_box_certified(q0, q1, ray, rx, ry, rz, fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
-				if (COUNT) ++lt;
-				int orig;
-				TriTest r = leaf_triangle_certified(p, ray, fastok, tmin, best + 2.0f * WINDOW, orig);
-				if (r.valid) {
-					any = true;
-					if (r.t < best) best = r.t;
-					if (!(r.t - best > WINDOW)) cand_insert(cl, best, r.t, orig, __float_as_int(q0.w));
-				}
+	}
+	// ---- leaves: certified reference box test, then the certified triangle test
+	while (pending != 0 || cur < 0) {
+		int leaf;
+		if (pending != 0) { leaf = pending; pending = 0; }
+		else { leaf = cur; cur = sp > 0 ? w.stack[--sp] : WALK_DONE; }
+		const int tri = leaf & 0x7fffffff;
+		const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
+		const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
+		if (COUNT) ++w.lr;
+		if (leaf_box_certified(q0, q1, ray, rx, ry, rz, w.fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
+			if (COUNT) ++w.lt;
+			int orig;
+			TriTest r = leaf_triangle_certified(p, ray, w.fastok, tmin, best + 2.0f * WINDOW, orig);
+			if (r.valid) {
+				if (r.t < best) best = r.t;
+				if (!(r.t - best > WINDOW)) cand_insert(w.cl, best, r.t, orig, __float_as_int(q0.w));
 			}
 		}
 	}
-	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); atomicAdd(cnt_nodes + 5, (unsigned long long)lr); }
-	hit.any = any;
-	if (cl.overflow || !cand_resolve(cl, best, hit)) {
+	w.cur = cur; w.sp = sp; w.pending = pending; w.best = best;
+}
+
+// The reference's (t, triangle) from the finished walk; rays the fast walk cannot decide are re-traced.
+template <bool COUNT>
+__device__ __forceinline__ void walk2_resolve(Walk2& w, const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
+                                              unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
+	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)w.ln); atomicAdd(cnt_tris, (unsigned long long)w.lt); atomicAdd(cnt_nodes + 5, (unsigned long long)w.lr); }
+	hit = HitRegs{FLT_MAX, -1, 0, false};
+	if (w.slow) {
+		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
+		return;
+	}
+	if (w.cl.overflow || !cand_resolve(w.cl, w.best, hit)) {
 		hit = HitRegs{FLT_MAX, -1, 0, false};
 		trace_canonical<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 	}
+	hit.any = hit.closest >= 0;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void trace_ordered2(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
+                                               unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
+	Walk2 w;
+	walk2_init(w, sc, ray);
+	while (!walk2_finished(w)) walk2_round<COUNT>(w, sc, ray, tmin);
+	walk2_resolve<COUNT>(w, sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 }
 
 // ------------------------------------------------------------------ 8-wide compressed traversal (experimental)

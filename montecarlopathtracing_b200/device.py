@@ -43,7 +43,7 @@ class Stats(ctypes.Structure):
 
 
 def library_path():
-    return os.path.join(_PKG_DIR, "libmcpt_cuda.so")
+    return os.environ.get("MCPT_LIB") or os.path.join(_PKG_DIR, "libmcpt_cuda.so")   # MCPT_LIB: development A/B builds
 
 
 def lib():

@@ -1,7 +1,7 @@
 #!/bin/bash
 # development A/B runs of the probe under different MCPT_OPT / MCPT_BLOCK settings
-for cfg in "0 128" "1 128" "0 64" "0 256" "1 64"; do
-  set -- $cfg
-  echo "=== MCPT_OPT=$1 MCPT_BLOCK=$2"
-  MCPT_OPT=$1 MCPT_BLOCK=$2 python tools/gpu_probe.py cbox diningroom 2>&1 | grep -E "fast:|render"
+for cfg in ${AB_CONFIGS:-"0,128 2,128"}; do
+  opt=${cfg%,*}; blk=${cfg#*,}
+  echo "=== MCPT_OPT=$opt MCPT_BLOCK=$blk"
+  MCPT_OPT=$opt MCPT_BLOCK=$blk timeout 300 python tools/gpu_probe.py ${AB_SCENES:-cbox diningroom} 2>&1 | grep -E "fast:|render|vs reference|Error|error"
 done
