@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--spp-per-step", type=int, default=8)
     ap.add_argument("--samples-in-flight", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--microbench-rays", type=int, default=1 << 24,
+                    help="rays per set of the intersection microbench (BASELINE configs[1] uses 64 Mi; 0 = skip)")
     return ap.parse_args()
 
 
@@ -161,6 +163,58 @@ def read_json(path):
 
 
 # ---------------------------------------------------------------------------- GPU arm
+def microbench(ctx, sc, a, torch):
+    """BASELINE configs[1]: coherent (the camera's own generator on a square grid) and random (origins uniform
+    in the scene box, directions uniform on the sphere) primary rays against the workload's BVH, device-resident
+    48-byte Ray in / 48-byte Hit out; closest-hit ids and t bits of FAST compared with the reference walk."""
+    from montecarlopathtracing_b200 import device, types as T
+    n = int(a.microbench_rays)
+    side = int(n ** 0.5)
+    n = side * side
+    res = {"rays_per_set": n, "scene": a.scene}
+    stream = torch.cuda.ExternalStream(ctx.stream)
+    d_hits = torch.empty(n * 48, dtype=torch.uint8, device="cuda")
+    d_ref = torch.empty(n * 48, dtype=torch.uint8, device="cuda")
+    d_closest = torch.empty(n, dtype=torch.int32, device="cuda")
+    d_closest_ref = torch.empty(n, dtype=torch.int32, device="cuda")
+    for label in ("coherent", "random"):
+        if label == "coherent":
+            with device.Context(side, side, 1, 1, device=torch.cuda.current_device()) as g:
+                g.set_camera(sc.camera)
+                g.generate_rays()
+                rays = torch.from_numpy(g.read_rays().view(np.uint8)).cuda()
+        else:
+            gen = torch.Generator(device="cuda").manual_seed(0x5EED0001)
+            lo = torch.tensor(sc.nodes["bbmin"][0][:3].astype(np.float32), device="cuda")
+            hi = torch.tensor(sc.nodes["bbmax"][0][:3].astype(np.float32), device="cuda")
+            r = torch.zeros(n, 12, dtype=torch.float32, device="cuda")
+            r[:, 0:3] = lo + (hi - lo) * torch.rand(n, 3, generator=gen, device="cuda")
+            z = 1 - 2 * torch.rand(n, generator=gen, device="cuda")
+            phi = 6.283185307179586 * torch.rand(n, generator=gen, device="cuda")
+            s_ = torch.sqrt(torch.clamp(1 - z * z, min=0))
+            r[:, 4], r[:, 5], r[:, 6] = s_ * torch.cos(phi), s_ * torch.sin(phi), z
+            rays = r.view(torch.uint8).reshape(-1)
+        best = 1e30
+        for it in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            ctx.trace_device(rays.data_ptr(), n, d_hits.data_ptr(), d_closest.data_ptr(), device.TRAVERSAL_FAST)
+            e1.record(stream)
+            e1.synchronize()
+            if it:
+                best = min(best, e0.elapsed_time(e1))
+        ctx.trace_device(rays.data_ptr(), n, d_ref.data_ptr(), d_closest_ref.data_ptr(), device.TRAVERSAL_REFERENCE)
+        ctx.synchronize()
+        t_a = d_hits.view(torch.int32).view(n, 12)[:, 8]
+        t_b = d_ref.view(torch.int32).view(n, 12)[:, 8]
+        res[label] = {"mrays_per_s": n / best / 1e3, "ms": best,
+                      "id_mismatches_vs_reference_walk": int((d_closest != d_closest_ref).sum().item()),
+                      "t_bit_mismatches_vs_reference_walk": int((t_a != t_b).sum().item()),
+                      "hit_fraction": float((d_closest >= 0).float().mean().item())}
+        del rays
+    return res
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -215,7 +269,10 @@ def run_b200(a):
     st = ctx.stats()
     nodes_per_ray = st["nodes_fetched"] / max(1, st["rays_traced"])
     tris_per_ray = st["tris_fetched"] / max(1, st["rays_traced"])
-    bytes_per_ray = nodes_per_ray * 64 + tris_per_ray * 64 + 96
+    leaves_per_ray = st["leaves_fetched"] / max(1, st["rays_traced"])
+    # 64 B inner node, 32 B leaf box (first two quads of the 96 B leaf record), 64 B more when the triangle is
+    # tested, 48 B path state in + 48 B out
+    bytes_per_ray = nodes_per_ray * 64 + leaves_per_ray * 32 + tris_per_ray * 64 + 96
     ctx.set_profiling(count_fetches=False, time_bounces=True)
 
     for _ in range(a.warmup):
@@ -297,12 +354,15 @@ def run_b200(a):
                          "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
                          "traffic": prof.get("dram_bytes_per_launch"),
-                         "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray,
+                         "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "leaves_per_ray": leaves_per_ray,
+                         "tris_per_ray": tris_per_ray,
                          "kernel_ms_per_step": bounce_ms_max / a.steps, "kernel_launches": int(bounce_launches),
                          "kernel_share_of_step": bounce_ms_max / ms_max,
                          "note": "algorithmic bytes are served mostly by L1/L2 (scene is L2-resident)"},
             "clocks": clk,
         }
+        if world == 1 and a.microbench_rays > 0:
+            out["microbench"] = microbench(ctx, sc, a, torch)
         if world == 1 and not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_sample(a)[0]
         print(json.dumps(out))

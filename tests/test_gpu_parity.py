@@ -77,6 +77,24 @@ def test_adversarial_rays_bit_exact(name, request):
             assert hit_mismatches(hits, ref_hits) == 0, trav
 
 
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_treelet_tree_bit_exact(name, request):
+    """bvhtype "treelet" (BVH/treeletBVH.cpp): another visit order, so other winners on ties - every
+    traversal must follow the tree it was given, as the reference's intersect kernel does."""
+    from montecarlopathtracing_b200 import host
+    sc = request.getfixturevalue(name)
+    nodes = host.treelet(sc.nodes)
+    rays = np.concatenate([random_rays(100_000, nodes, seed=9), adversarial_rays(sc, 30_000)])
+    ref_hits, ref_closest = O.intersect(rays, nodes, sc.triangles)
+    with device.Context(64, 64, max_depth=8, max_attempt=16) as ctx:
+        ctx.upload_scene(sc.triangles, sc.materials, nodes)
+        ctx.set_camera(sc.camera)
+        for trav in ALL_TRAVERSALS:
+            hits, closest = ctx.trace(rays, trav)
+            assert np.array_equal(closest, ref_closest), trav
+            assert hit_mismatches(hits, ref_hits) == 0, trav
+
+
 def test_trace_edge_cases(cbox):
     with _ctx(cbox, 64, 64) as ctx:
         hits, closest = ctx.trace(np.zeros(0, T.RAY))           # empty batch

@@ -65,6 +65,64 @@ def test_bvh_random_triangles_equal_reference(n):
     assert ours.tobytes() == ref.tobytes()
 
 
+def _ref_treelet(R, nodes):
+    out = np.zeros(len(nodes), T.BVH_NODE)
+    src = np.ascontiguousarray(nodes)
+    assert R.ref_treelet(src.ctypes.data_as(ctypes.c_void_p), len(src), out.ctypes.data_as(ctypes.c_void_p)) == len(src)
+    return out
+
+
+@pytest.mark.parametrize("name", ["cbox", "veach_mis"])
+def test_treelet_memcmp_equal_to_reference(name):
+    """bvhtype "treelet": our CPU optimiser == BVH::TreeletBVH<CPU> on the same LBVH, byte for byte."""
+    R = _ref()
+    sc = scenes.load(name)
+    ours = host.treelet(sc.nodes)
+    assert ours.tobytes() == _ref_treelet(R, sc.nodes).tobytes()
+    assert ours.tobytes() != sc.nodes.tobytes()          # it did restructure something
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 7, 8, 17, 100, 1000, 5000])
+def test_treelet_random_triangles_equal_reference(n):
+    R = _ref()
+    rng = np.random.default_rng(100 + n)
+    tris = np.zeros(n, T.TRIANGLE)
+    c = rng.uniform(-10, 10, (n, 1, 3))
+    tris["v"][:, :, :3] = (c + rng.normal(0, 0.5, (n, 3, 3))).astype(np.float32)
+    lbvh = host.build_bvh(tris)
+    # the reference's SAH pass reads node #<triangle id of the first leaf> (treeletBVH.cpp:303); it does not
+    # terminate when that node is an ancestor of the first leaf, so only compare where it does
+    first = int(lbvh[n - 1]["left"])
+    p, anc = int(lbvh[n - 1]["parent"]), {n - 1}
+    while p != -1:
+        anc.add(p)
+        p = int(lbvh[p]["parent"])
+    if first in anc:
+        with pytest.raises(RuntimeError):
+            host.treelet(lbvh)
+        return
+    assert host.treelet(lbvh).tobytes() == _ref_treelet(R, lbvh).tobytes()
+    assert host.build_bvh(tris, "treelet").tobytes() == host.treelet(lbvh).tobytes()
+
+
+def test_treelet_keeps_a_valid_tree(cbox):
+    nd = host.treelet(cbox.nodes)
+    n = len(cbox.triangles)
+    seen = np.zeros(len(nd), bool)
+    stack = [0]
+    while stack:
+        i = stack.pop()
+        assert not seen[i]
+        seen[i] = True
+        if i < n - 1:
+            for c in (int(nd[i]["left"]), int(nd[i]["right"])):
+                assert int(nd[c]["parent"]) == i
+                assert np.all(nd[c]["bbmin"][:3] >= nd[i]["bbmin"][:3]) and np.all(nd[c]["bbmax"][:3] <= nd[i]["bbmax"][:3])
+                stack.append(c)
+    assert seen.all()
+    assert sorted(int(x) for x in nd[n - 1:]["left"]) == list(range(n))
+
+
 def test_bvh_structure_invariants(cbox):
     nd = cbox.nodes
     n = len(cbox.triangles)
