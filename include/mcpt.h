@@ -75,7 +75,9 @@ typedef struct mcpt_stats {
 	uint64_t kernel_launches; /* CUDA kernels launched by this context */
 	uint64_t nodes_fetched;   /* inner-node records fetched (instrumented kernels only: mcpt_trace_count, profiling) */
 	uint64_t tris_fetched;    /* exact triangle tests */
-	uint64_t leaves_fetched;  /* leaf records fetched (FAST / ORDERED2; the other walks read leaf boxes from nodes) */
+	uint64_t leaves_fetched;  /* leaf records fetched (FAST; the other walks read leaf boxes from nodes) */
+	uint64_t slow_rays;       /* FAST only: rays handed to the reference walk (zero direction component, far origin, ...) */
+	uint64_t replayed_rays;   /* FAST only: rays re-traced by the canonical walk (candidate in the tie band, overflow) */
 } mcpt_stats;
 
 const char* mcpt_last_error(void);

@@ -333,4 +333,60 @@ void build_wide_bvh8(const std::vector<DNode>& bvh2, const DLeaf* leaves, int nt
 	}
 }
 
+// ------------------------------------------------------------------ 15-bit scene-grid nodes
+bool build_qnodes(const std::vector<DNode>& bvh2, std::vector<QNode>& out, QFrame& fr) {
+	out.clear();
+	if (bvh2.empty()) return false;
+	// frame = box of the root's two children, padded so that margins never clip
+	const DNode& r = bvh2[0];
+	double lo[3] = {std::min(r.lminx, r.rminx), std::min(r.lminy, r.rminy), std::min(r.lminz, r.rminz)};
+	double hi[3] = {std::max(r.lmaxx, r.rmaxx), std::max(r.lmaxy, r.rmaxy), std::max(r.lmaxz, r.rmaxz)};
+	double ext = 0.0;
+	for (int a = 0; a < 3; ++a) {
+		if (!(lo[a] <= hi[a]) || !std::isfinite(lo[a]) || !std::isfinite(hi[a])) return false;
+		ext = std::max(ext, hi[a] - lo[a]);
+	}
+	if (!(ext > 0.0) || !(ext < 1e30)) return false;
+	// ONE step for all axes: the error budget of the device arithmetic is in units of (distance of the ray origin
+	// from the frame) / step, so a finer grid on a flat axis would only shrink the set of rays that may use it
+	const float step = float(ext / double(QNODE_GRID - 4 * (QNODE_MARGIN + 2)));
+	if (!(step > 0.0f)) return false;
+	for (int a = 0; a < 3; ++a) {
+		fr.lo[a] = float(lo[a] - double(step) * 2 * (QNODE_MARGIN + 2));
+		fr.step[a] = step;
+		if (!std::isfinite(fr.lo[a])) return false;
+	}
+	fr.extent = float(ext);
+	out.resize(bvh2.size());
+	bool ok = true;
+	auto qlo = [&](float p, int a) {          // largest grid plane <= p - MARGIN steps
+		const double g = (double(p) - double(fr.lo[a])) / double(fr.step[a]);
+		long q = long(std::floor(g)) - QNODE_MARGIN;
+		while (q > 0 && double(fr.lo[a]) + double(q) * double(fr.step[a]) > double(p) - QNODE_MARGIN * double(fr.step[a])) --q;
+		if (q < 0 || q > QNODE_GRID) ok = false;
+		return uint32_t(std::min<long>(std::max<long>(q, 0), QNODE_GRID));
+	};
+	auto qhi = [&](float p, int a) {          // smallest grid plane >= p + MARGIN steps
+		const double g = (double(p) - double(fr.lo[a])) / double(fr.step[a]);
+		long q = long(std::ceil(g)) + QNODE_MARGIN;
+		while (q < QNODE_GRID && double(fr.lo[a]) + double(q) * double(fr.step[a]) < double(p) + QNODE_MARGIN * double(fr.step[a])) ++q;
+		if (q < 0 || q > QNODE_GRID) ok = false;
+		return uint32_t(std::min<long>(std::max<long>(q, 0), QNODE_GRID));
+	};
+	for (size_t i = 0; i < bvh2.size(); ++i) {
+		const DNode& n = bvh2[i];
+		QNode& q = out[i];
+		q.planes[0] = qlo(n.lminx, 0) | (qhi(n.lmaxx, 0) << 16);
+		q.planes[1] = qlo(n.lminy, 1) | (qhi(n.lmaxy, 1) << 16);
+		q.planes[2] = qlo(n.lminz, 2) | (qhi(n.lmaxz, 2) << 16);
+		q.planes[3] = qlo(n.rminx, 0) | (qhi(n.rmaxx, 0) << 16);
+		q.planes[4] = qlo(n.rminy, 1) | (qhi(n.rmaxy, 1) << 16);
+		q.planes[5] = qlo(n.rminz, 2) | (qhi(n.rmaxz, 2) << 16);
+		q.left = n.left;
+		q.right = n.right;
+	}
+	if (!ok) out.clear();
+	return ok;
+}
+
 }  // namespace mcpt

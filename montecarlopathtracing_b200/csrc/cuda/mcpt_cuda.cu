@@ -44,6 +44,10 @@ struct DevBuf {
 		p = nullptr;
 		n = 0;
 	}
+	DevBuf() = default;
+	DevBuf(const DevBuf&) = delete;
+	DevBuf& operator=(const DevBuf&) = delete;
+	~DevBuf() { release(); }
 };
 
 }  // namespace
@@ -59,8 +63,11 @@ struct mcpt_ctx {
 	// scene
 	DevBuf<mcpt_bvh_node> nodes_ref;
 	DevBuf<mcpt_triangle> tris_ref;
-	DevBuf<DNode> nodes, fast_nodes;
-	DevBuf<DLeaf> leaves, wleaves;
+	DevBuf<DNode> nodes;
+	DevBuf<DLeaf> wleaves;
+	DevBuf<unsigned char> hot;        // fast-walk nodes followed by the leaf records: ONE range, so that one L2 access-policy window covers it
+	DNode* fast_nodes = nullptr;
+	DLeaf* leaves = nullptr;
 	DevBuf<WNode> wnodes;
 	DevBuf<mcpt_material> mats;
 	DevBuf<float2> cs_table;
@@ -436,25 +443,70 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	CU(cudaMemcpyAsync(c->wnodes.p, wide.data(), sizeof(WNode) * wide.size(), cudaMemcpyHostToDevice, c->stream));
 	if (!wide_leaves.empty())
 		CU(cudaMemcpyAsync(c->wleaves.p, wide_leaves.data(), sizeof(DLeaf) * wide_leaves.size(), cudaMemcpyHostToDevice, c->stream));
-	CU(c->fast_nodes.alloc(fast.size()));
-	CU(cudaMemcpyAsync(c->fast_nodes.p, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
+	std::vector<QNode> qn;
+	QFrame qframe{};
+#if MCPT_QNODES
+	const bool have_q = !root_leaf && build_qnodes(fast, qn, qframe);
+#else
+	const bool have_q = false;
+#endif
+#if MCPT_LEAF_LINKS
+	for (DNode& n : fast) {      // after the derived builds, which read the ~triangle form
+		if (n.left < 0) n.left = int32_t(0x80000000u | uint32_t(~n.left));
+		if (n.right < 0) n.right = int32_t(0x80000000u | uint32_t(~n.right));
+	}
+	for (QNode& n : qn) {
+		if (n.left < 0) n.left = int32_t(0x80000000u | uint32_t(~n.left));
+		if (n.right < 0) n.right = int32_t(0x80000000u | uint32_t(~n.right));
+	}
+#endif
+	const size_t hot_nodes_bytes = (sizeof(DNode) * fast.size() + 255) / 256 * 256;
+	const size_t hot_leaf_bytes = (sizeof(DLeaf) * size_t(ntris) + 255) / 256 * 256;
+	const size_t hot_bytes = hot_nodes_bytes + hot_leaf_bytes + sizeof(QNode) * std::max<size_t>(1, qn.size());
+	CU(c->hot.alloc(hot_bytes));
+	c->fast_nodes = reinterpret_cast<DNode*>(c->hot.p);
+	c->leaves = reinterpret_cast<DLeaf*>(c->hot.p + hot_nodes_bytes);
+	QNode* d_qnodes = reinterpret_cast<QNode*>(c->hot.p + hot_nodes_bytes + hot_leaf_bytes);
+	CU(cudaMemcpyAsync(c->fast_nodes, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
+	if (have_q) CU(cudaMemcpyAsync(d_qnodes, qn.data(), sizeof(QNode) * qn.size(), cudaMemcpyHostToDevice, c->stream));
 	CU(c->nodes_ref.alloc(nnodes));
 	CU(c->tris_ref.alloc(ntris));
 	CU(c->nodes.alloc(dn.size()));
-	CU(c->leaves.alloc(ntris));
 	CU(c->mats.alloc(nmats));
 	CU(c->cs_table.alloc(32768));
 	CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->nodes.p, dn.data(), sizeof(DNode) * dn.size(), cudaMemcpyHostToDevice, c->stream));
-	CU(cudaMemcpyAsync(c->leaves.p, dt.data(), sizeof(DLeaf) * ntris, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->leaves, dt.data(), sizeof(DLeaf) * ntris, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaMemcpyAsync(c->cs_table.p, cs.data(), sizeof(float2) * 32768, cudaMemcpyHostToDevice, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	c->force_reference = !contained;
+	float max_abs = 0.0f;
+	for (float v : {nodes[0].bbmin.x, nodes[0].bbmin.y, nodes[0].bbmin.z, nodes[0].bbmax.x, nodes[0].bbmax.y, nodes[0].bbmax.z})
+		max_abs = std::max(max_abs, std::fabs(v));
+	if (!(max_abs < 1e30f) || (MCPT_QNODES && !have_q && !root_leaf)) c->force_reference = true;   // no grid frame: degenerate scene
+	// Keep the walk's working set resident in L2: the per-bounce ray / path-state streams (hundreds of MB)
+	// otherwise evict it, and every evicted node costs a whole warp a DRAM round trip (ncu: 20% L2 misses,
+	// 0.6 DRAM node fetches per ray).  Measured on B200: no gain (-1%), so it is opt-in: MCPT_OPT bit 2.
+	if (c->opt_flags & 4) {
+		cudaDeviceProp prop;
+		CU(cudaGetDeviceProperties(&prop, c->prm.device));
+		const size_t carve = std::min<size_t>(size_t(prop.persistingL2CacheMaxSize), hot_bytes);
+		if (carve > 0 && prop.accessPolicyMaxWindowSize > 0) {
+			CU(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve));
+			cudaStreamAttrValue attr{};
+			attr.accessPolicyWindow.base_ptr = c->hot.p;
+			attr.accessPolicyWindow.num_bytes = std::min<size_t>(hot_bytes, size_t(prop.accessPolicyMaxWindowSize));
+			attr.accessPolicyWindow.hitRatio = float(std::min(1.0, double(carve) / double(attr.accessPolicyWindow.num_bytes)));
+			attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+			attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+			CU(cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+		}
+	}
 	c->cache_tris.assign(tris, tris + ntris);
 	c->cache_nodes.assign(nodes, nodes + nnodes);
-	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes.p, c->wnodes.p, c->wleaves.p, c->leaves.p, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags};
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs, have_q ? d_qnodes : nullptr, qframe};
 	c->have_scene = true;
 	return MCPT_OK;
 }
@@ -651,7 +703,7 @@ int mcpt_trace_count(mcpt_ctx* c, const mcpt_ray* d_rays, long n, int traversal)
 	if (!d_rays || n <= 0) return fail(MCPT_ERR_ARG, "mcpt_trace_count: bad arguments");
 	if (c->t_hits.n < size_t(n)) CU(c->t_hits.alloc(n));
 	CU(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * 3, c->stream));
-	CU(cudaMemsetAsync(c->counters.p + 5, 0, sizeof(unsigned long long), c->stream));
+	CU(cudaMemsetAsync(c->counters.p + 5, 0, sizeof(unsigned long long) * 3, c->stream));
 	if (int r = launch_intersect(c, d_rays, n, c->t_hits.p, nullptr, traversal, true)) return r;
 	CU(cudaStreamSynchronize(c->stream));
 	return MCPT_OK;
@@ -706,6 +758,8 @@ int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
 	out->nodes_fetched = h[0];
 	out->tris_fetched = h[1];
 	out->leaves_fetched = h[5];
+	out->slow_rays = h[6];
+	out->replayed_rays = h[7];
 	out->rays_traced = h[2] + h[3];
 	out->paths = h[4] + c->stage_paths;
 	out->kernel_launches = c->launches;

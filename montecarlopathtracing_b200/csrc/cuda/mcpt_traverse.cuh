@@ -38,7 +38,25 @@ struct SceneDev {
 	int ntris, nnodes;
 	int root_is_leaf;
 	int opt_flags;               // development switches (MCPT_OPT): bit 1 = one-thread-per-ray kernels instead of persistent ones
+	float max_abs;               // largest |coordinate| of the scene's bounding box (finite-arithmetic guard of the fast walk)
+	const QNode* qnodes;         // 15-bit grid version of fast_nodes (null: not available)
+	QFrame qframe;
 };
+
+// 256-bit read-only loads (LDG.E.256, sm_100): a divergent warp costs the L1 one wavefront per lane PER
+// LOAD INSTRUCTION, and this kernel is bound by exactly that, so a 64 B node is two loads instead of four.
+#ifndef MCPT_LDG256
+#define MCPT_LDG256 1
+#endif
+__device__ __forceinline__ void ldg256(const float4* p, float4& lo, float4& hi) {
+#if MCPT_LDG256
+	asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+	             : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+	             : "l"(p));
+#else
+	lo = __ldg(p); hi = __ldg(p + 1);
+#endif
+}
 
 struct HitRegs {
 	float t;
@@ -245,7 +263,9 @@ __device__ __forceinline__ bool leaf_box_certified(const float4& q0, const float
 // they can be neither near candidates nor band members.
 __device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restrict__ p, const RayRegs& ray, bool fastok, float tmin,
                                                            float tfar_skip, int& orig_tri) {
-	const float4 q2 = __ldg(p + 2), q3 = __ldg(p + 3), q4 = __ldg(p + 4), q5 = __ldg(p + 5);
+	float4 q2, q3, q4, q5;
+	ldg256(p + 2, q2, q3);
+	ldg256(p + 4, q4, q5);
 	orig_tri = __float_as_int(q5.w);
 	TriTest out{0.0f, false};
 	const float a1 = ray.direction.x, a2 = ray.direction.y, a3 = ray.direction.z;
@@ -284,7 +304,7 @@ __device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restr
 	if (ambiguous)
 		return intersect_triangle(ray, q2.x, q2.y, q2.z, e1x, e1y, e1z, e2x, e2y, e2z, q5.x, q5.y, q5.z, q2.w, q3.w, q4.w, tmin);
 	// b, c and b + c certainly pass: the reference's t, with its exact operations (objdef.h:203-207)
-	const float s0 = q5.x / det, s4 = -q5.y / det, s8 = q5.z / det;
+	const float s0 = fdiv(q5.x, det), s4 = fdiv(-q5.y, det), s8 = fdiv(q5.z, det);
 	const float t = Ax * s0 + Ay * s4 + Az * s8;
 	if (t <= tmin) return out;
 	out.t = t;
@@ -311,6 +331,15 @@ __device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restr
 constexpr float WINDOW = 2.0e-5f;
 constexpr float BAND = 9.9e-6f;
 constexpr int LEAF_FLAG = int(0x80000000);
+#ifndef MCPT_FUSED_SLAB
+#define MCPT_FUSED_SLAB 1
+#endif
+#ifndef MCPT_QNODES
+#define MCPT_QNODES 0     // 32 B grid-quantised inner nodes: measured SLOWER on B200 (-30% path tracing, -37% coherent rays):
+#endif                    // the PRMT decodes land on the ALU pipe, which min/max and compares already saturate
+#ifndef MCPT_LEAF_LINKS
+#define MCPT_LEAF_LINKS 1 // fast nodes store leaf links as LEAF_FLAG | triangle (no decode in the loop)
+#endif
 #ifndef MCPT_POSTPONE_LEAF
 #define MCPT_POSTPONE_LEAF 1
 #endif
@@ -371,6 +400,12 @@ struct Walk2 {
 	int sp, cur, pending;      // pending: postponed leaf (0 = none; leaf codes carry LEAF_FLAG, so they are never 0)
 	float best;
 	float rx, ry, rz;
+#if MCPT_FUSED_SLAB
+	float c1x, c1y, c1z, c2x, c2y, c2z;   // plane distance = fma(plane, r, c): c1 for bmin planes, c2 for bmax planes
+#endif
+#if MCPT_QNODES
+	float qax, qay, qaz, qbx, qby, qbz;   // plane distance = fma(2^15 + q, qb, qa)
+#endif
 	CandList cl;
 	bool fastok, slow;         // slow: zero direction component or single-triangle scene -> reference walk
 	unsigned ln, lt, lr;       // instrumentation
@@ -381,6 +416,42 @@ __device__ __forceinline__ void walk2_init(Walk2& w, const SceneDev& sc, const R
 	w.slow = ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf;
 	w.rx = 1.0f / ray.direction.x; w.ry = 1.0f / ray.direction.y; w.rz = 1.0f / ray.direction.z;
 	w.fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
+#if MCPT_FUSED_SLAB
+	{
+		// -o*r with the rounding error of the fused form (<= 2.1 * 2^-24 |o*r| per plane, see walk2_round) folded
+		// in: bmin planes are the near ones when r > 0, so c1 moves them down and c2 moves the bmax planes up by
+		// S = 2^-22 |o*r|; for r < 0 the roles (and the signs) swap.  The slack is per axis: an axis the ray is
+		// almost parallel to gets a huge S, but only its own (already huge) plane distances see it.
+		const float ox = ray.origin.x * w.rx, oy = ray.origin.y * w.ry, oz = ray.origin.z * w.rz;
+		const float sx = copysignf(0x1p-22f * fabsf(ox), w.rx), sy = copysignf(0x1p-22f * fabsf(oy), w.ry),
+		            sz = copysignf(0x1p-22f * fabsf(oz), w.rz);
+		w.c1x = -ox - sx; w.c2x = -ox + sx;
+		w.c1y = -oy - sy; w.c2y = -oy + sy;
+		w.c1z = -oz - sz; w.c2z = -oz + sz;
+		// everything must stay finite (no Inf - Inf): tiny direction components or far-away origins walk the reference way
+		const float big = fmaxf(fmaxf(fabsf(ox), fabsf(oy)), fabsf(oz)) +
+		                  sc.max_abs * fmaxf(fmaxf(fabsf(w.rx), fabsf(w.ry)), fabsf(w.rz));
+		w.slow = w.slow || !w.fastok || !(big < 1e37f);
+	}
+#endif
+#if MCPT_QNODES
+	{
+		// Grid plane q of axis a lies at lo + q * step, so its distance is q * (step / d) + (lo - o) / d.  q arrives
+		// as the float M = 2^15 + q (one PRMT, see walk2_round), hence qa = (lo - o) / d - 2^15 qb.
+		// Error budget, in units of |step / d| (e = 2^-24, k = |lo - o| / scene extent, grid = 2^15 steps per extent):
+		//   qb, q * qb: 2e q <= 2^-8;  (lo - o) * r: 3e * 2^15 k;  qa's subtraction and the final fma: 2 * e * 2^15 (k + 1);
+		//   the reference's own fl(fl(p - o) / d) on the true plane: 2e * 2^15 (k + 1).
+		// For k <= 32 that is < 0.45 steps in total; the builder rounds outwards and adds QNODE_MARGIN = 2 steps, so a box
+		// the reference's test accepts is always accepted here.  Rays farther than 32 extents from the frame, or whose
+		// arithmetic could overflow, take the reference walk.
+		const float ux = sc.qframe.lo[0] - ray.origin.x, uy = sc.qframe.lo[1] - ray.origin.y, uz = sc.qframe.lo[2] - ray.origin.z;
+		w.qbx = sc.qframe.step[0] * w.rx; w.qby = sc.qframe.step[1] * w.ry; w.qbz = sc.qframe.step[2] * w.rz;
+		w.qax = ux * w.rx - 32768.0f * w.qbx; w.qay = uy * w.ry - 32768.0f * w.qby; w.qaz = uz * w.rz - 32768.0f * w.qbz;
+		const float far = fmaxf(fmaxf(fabsf(ux), fabsf(uy)), fabsf(uz));
+		const float big = (far + 2.0f * sc.qframe.extent) * fmaxf(fmaxf(fabsf(w.rx), fabsf(w.ry)), fabsf(w.rz));
+		w.slow = w.slow || !w.fastok || !(far <= 32.0f * sc.qframe.extent) || !(big < 1e37f);
+	}
+#endif
 	w.sp = 0;
 	w.cur = w.slow ? WALK_DONE : 0;
 	w.pending = 0;
@@ -397,12 +468,67 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 	const float rx = w.rx, ry = w.ry, rz = w.rz;
 	int cur = w.cur, sp = w.sp, pending = w.pending;
 	float best = w.best;
+#if MCPT_FUSED_SLAB || MCPT_QNODES
+	const float tminlo = tmin * (1.0f - 0x1p-19f);
+#endif
+	// per-ray constants are copied out of `w` (which lives in local memory because of its stack array): read
+	// through `w` inside the loop they would be reloaded after every stack store
+#if MCPT_QNODES
+	const float qax = w.qax, qay = w.qay, qaz = w.qaz, qbx = w.qbx, qby = w.qby, qbz = w.qbz;
+	const unsigned snx = qbx < 0.0f ? 0x7324u : 0x7104u, sny = qby < 0.0f ? 0x7324u : 0x7104u, snz = qbz < 0.0f ? 0x7324u : 0x7104u;
+	const unsigned sfx = snx ^ 0x0220u, sfy = sny ^ 0x0220u, sfz = snz ^ 0x0220u;
+#elif MCPT_FUSED_SLAB
+	const float c1x = w.c1x, c1y = w.c1y, c1z = w.c1z, c2x = w.c2x, c2y = w.c2y, c2z = w.c2z;
+#endif
 	// ---- inner nodes: conservative tests of both children, near child first
 	while (cur >= 0 && cur != WALK_DONE) {
-		const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
-		float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-		int4 link = __ldg(reinterpret_cast<const int4*>(p + 3));
+#if MCPT_QNODES
+		float4 qa_, qb_;
+		ldg256(reinterpret_cast<const float4*>(sc.qnodes + cur), qa_, qb_);
+		const int2 link = make_int2(__float_as_int(qb_.z), __float_as_int(qb_.w));
 		if (COUNT) ++w.ln;
+		const float tprune = __fmaf_rn(best, PRUNE_REL, PRUNE_ABS);
+		// 2^15 + q as a float: the two bytes of q land in mantissa bits 8..22 under the exponent byte 0x47.  The same
+		// PRMT picks the NEAR or the FAR plane of the axis (low half = min plane, high half = max plane; which one is
+		// near depends only on the sign of the ray direction), so no min/max per axis is needed.
+		#define QSEL(word, sel) __uint_as_float(__byte_perm(__float_as_uint(word), 0x47000000u, sel))
+		const float loL = fmaxf(fmaxf(__fmaf_rn(QSEL(qa_.x, snx), qbx, qax), __fmaf_rn(QSEL(qa_.y, sny), qby, qay)), __fmaf_rn(QSEL(qa_.z, snz), qbz, qaz));
+		const float tfL = fminf(fminf(__fmaf_rn(QSEL(qa_.x, sfx), qbx, qax), __fmaf_rn(QSEL(qa_.y, sfy), qby, qay)), __fmaf_rn(QSEL(qa_.z, sfz), qbz, qaz));
+		const float loR = fmaxf(fmaxf(__fmaf_rn(QSEL(qa_.w, snx), qbx, qax), __fmaf_rn(QSEL(qb_.x, sny), qby, qay)), __fmaf_rn(QSEL(qb_.y, snz), qbz, qaz));
+		const float tfR = fminf(fminf(__fmaf_rn(QSEL(qa_.w, sfx), qbx, qax), __fmaf_rn(QSEL(qb_.x, sfy), qby, qay)), __fmaf_rn(QSEL(qb_.y, sfz), qbz, qaz));
+		#undef QSEL
+		// all evaluation error is inside the builder's outward margin (walk2_init); tmin only needs its own ulp
+		const bool hitL = !((tfL < loL) || (tfL < tminlo) || (loL > tprune));
+		const bool hitR = !((tfR < loR) || (tfR < tminlo) || (loR > tprune));
+#else
+		const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
+		float4 a, b, c, lk;
+		ldg256(p, a, b);
+		ldg256(p + 2, c, lk);
+		const int2 link = make_int2(__float_as_int(lk.x), __float_as_int(lk.y));
+		if (COUNT) ++w.ln;
+#endif
+#if MCPT_QNODES
+#elif MCPT_FUSED_SLAB
+		// plane distance as ONE fma(plane, 1/d, -o/d -+ S).  Against the reference's fl(fl(plane - o) / d) = T:
+		// |t - T| <= 4.1 * 2^-24 |T| + 2.1 * 2^-24 |o/d|; the second (absolute) part is already inside c1/c2, the
+		// relative part is the 2^-20 max(|tn|, |tf|) below.  The tmin and pruning tests take their relative slack
+		// from constants (tminlo = tmin (1 - 2^-19); the 2^-7 pruning margin dwarfs 2^-20).
+		const float tprune = __fmaf_rn(best, PRUNE_REL, PRUNE_ABS);
+		float o1, o2, n0, n1, n2, f0, f1, f2;
+		o1 = __fmaf_rn(a.x, rx, c1x); o2 = __fmaf_rn(a.w, rx, c2x); n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
+		o1 = __fmaf_rn(a.y, ry, c1y); o2 = __fmaf_rn(b.x, ry, c2y); n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
+		o1 = __fmaf_rn(a.z, rz, c1z); o2 = __fmaf_rn(b.y, rz, c2z); n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
+		const float tnL = fmaxf(fmaxf(n0, n1), n2), tfL = fminf(fminf(f0, f1), f2);
+		o1 = __fmaf_rn(b.z, rx, c1x); o2 = __fmaf_rn(c.y, rx, c2x); n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
+		o1 = __fmaf_rn(b.w, ry, c1y); o2 = __fmaf_rn(c.z, ry, c2y); n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
+		o1 = __fmaf_rn(c.x, rz, c1z); o2 = __fmaf_rn(c.w, rz, c2z); n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
+		const float tnR = fmaxf(fmaxf(n0, n1), n2), tfR = fminf(fminf(f0, f1), f2);
+		const float loL = __fmaf_rn(fmaxf(fabsf(tnL), fabsf(tfL)), -SLAB_SLACK, tnL);
+		const float loR = __fmaf_rn(fmaxf(fabsf(tnR), fabsf(tfR)), -SLAB_SLACK, tnR);
+		const bool hitL = !((tfL < loL) || (tfL < tminlo) || (tnL > tprune));
+		const bool hitR = !((tfR < loR) || (tfR < tminlo) || (tnR > tprune));
+#else
 		const float tprune = best * PRUNE_REL + PRUNE_ABS;
 		// (bb - o) * (1/d): |computed - reference| <= 2^-22 |t|, covered 4x by the 2^-20 relative slack.  (A single
 		// fused bb*(1/d) - o*(1/d) is cheaper but its error scales with |o/d|: rays nearly parallel to an axis
@@ -422,8 +548,13 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		// comparisons are false on NaN => not rejected (conservative)
 		const bool hitL = !((tfL < loL) || (tfL < tmin - sL) || (loL > tprune));
 		const bool hitR = !((tfR < loR) || (tfR < tmin - sR) || (loR > tprune));
+#endif
+#if MCPT_LEAF_LINKS
+		const int cl_ = link.x, cr_ = link.y;
+#else
 		int cl_ = link.x < 0 ? (LEAF_FLAG | ~link.x) : link.x;
 		int cr_ = link.y < 0 ? (LEAF_FLAG | ~link.y) : link.y;
+#endif
 		if (hitL && hitR) {
 			const bool swap = loR < loL;
 			const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
@@ -445,7 +576,8 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		else { leaf = cur; cur = sp > 0 ? w.stack[--sp] : WALK_DONE; }
 		const int tri = leaf & 0x7fffffff;
 		const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
-		const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
+		float4 q0, q1;
+		ldg256(p, q0, q1);
 		if (COUNT) ++w.lr;
 		if (leaf_box_certified(q0, q1, ray, rx, ry, rz, w.fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
 			if (COUNT) ++w.lt;
@@ -467,10 +599,12 @@ __device__ __forceinline__ void walk2_resolve(Walk2& w, const SceneDev& sc, cons
 	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)w.ln); atomicAdd(cnt_tris, (unsigned long long)w.lt); atomicAdd(cnt_nodes + 5, (unsigned long long)w.lr); }
 	hit = HitRegs{FLT_MAX, -1, 0, false};
 	if (w.slow) {
+		if (COUNT) atomicAdd(cnt_nodes + 6, 1ull);
 		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 		return;
 	}
 	if (w.cl.overflow || !cand_resolve(w.cl, w.best, hit)) {
+		if (COUNT) atomicAdd(cnt_nodes + 7, 1ull);
 		hit = HitRegs{FLT_MAX, -1, 0, false};
 		trace_canonical<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 	}

@@ -39,7 +39,8 @@ class Params(ctypes.Structure):
 class Stats(ctypes.Structure):
     _fields_ = [("rays_traced", ctypes.c_uint64), ("paths", ctypes.c_uint64), ("kernel_launches", ctypes.c_uint64),
                 ("nodes_fetched", ctypes.c_uint64), ("tris_fetched", ctypes.c_uint64),
-                ("leaves_fetched", ctypes.c_uint64)]
+                ("leaves_fetched", ctypes.c_uint64),
+                ("slow_rays", ctypes.c_uint64), ("replayed_rays", ctypes.c_uint64)]
 
 
 def library_path():

@@ -46,8 +46,9 @@ def main():
                     ctx.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr(), d_closest.data_ptr(), trav)
                     ctx.synchronize()
                     res[tn] = (d_hits.cpu().numpy().copy(), d_closest.cpu().numpy().copy())
-                    print("%s %s %s: %.3f ms  %.1f Mrays/s  nodes/ray %.2f leaves/ray %.2f tris/ray %.2f" % (
-                        name, label, tn, ms, n / ms / 1e3, st["nodes_fetched"] / n, st["leaves_fetched"] / n, st["tris_fetched"] / n), flush=True)
+                    print("%s %s %s: %.3f ms  %.1f Mrays/s  nodes/ray %.2f leaves/ray %.2f tris/ray %.2f slow %d replayed %d" % (
+                        name, label, tn, ms, n / ms / 1e3, st["nodes_fetched"] / n, st["leaves_fetched"] / n, st["tris_fetched"] / n,
+                        st["slow_rays"], st["replayed_rays"]), flush=True)
                 h0 = res["reference"][0].view(T.HIT); h1 = res["fast"][0].view(T.HIT)
                 bad = int((res["reference"][1] != res["fast"][1]).sum())
                 badt = int((h0["t"].view(np.uint32) != h1["t"].view(np.uint32)).sum())
