@@ -12,9 +12,9 @@ work is fixed, ranks own disjoint sample indices, scene + BVH replicated).
   e2e        the same metric through the C ABI with HOST buffers: every step uploads the scene from
              pinned host memory (mcpt_upload_scene + mcpt_set_camera), renders, and reads the merged
              sums back to the host (mcpt_read_sums); wall clock around the calls.
-  roofline   the dominant kernel k_wave_bounce<FAST>: algorithmic bytes per ray (nodes and triangles
-             fetched, counted by an instrumented pass of the same kernel, x 64 B + 96 B path state)
-             x rays / summed CUDA-event time of the bounce launches, against the measured HBM copy
+  roofline   the dominant kernel k_wave_trace_persistent (the BVH walk of one bounce): algorithmic bytes
+             per ray (nodes, leaf boxes and triangles fetched, counted by an instrumented pass of the same
+             walk, + 40 B ray in / hit out) x rays / summed CUDA-event time of its launches, against the measured HBM copy
              bandwidth (MEASURED_PEAKS.json).  The scene is L2-resident, so frac can exceed what HBM
              traffic alone would allow; traffic (ncu dram bytes per launch) is read from profiles/.
   cpu_baseline / --impl reference: the CPU oracle (a line-by-line port of the reference's OpenCL
@@ -271,8 +271,8 @@ def run_b200(a):
     tris_per_ray = st["tris_fetched"] / max(1, st["rays_traced"])
     leaves_per_ray = st["leaves_fetched"] / max(1, st["rays_traced"])
     # 64 B inner node, 32 B leaf box (first two quads of the 96 B leaf record), 64 B more when the triangle is
-    # tested, 48 B path state in + 48 B out
-    bytes_per_ray = nodes_per_ray * 64 + leaves_per_ray * 32 + tris_per_ray * 64 + 96
+    # tested, 32 B ray in (origin, direction) + 8 B hit record out
+    bytes_per_ray = nodes_per_ray * 64 + leaves_per_ray * 32 + tris_per_ray * 64 + 40
     ctx.set_profiling(count_fetches=False, time_bounces=True)
 
     for _ in range(a.warmup):
@@ -350,7 +350,7 @@ def run_b200(a):
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": t2.item() / a.steps * 1e3},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_wave_bounce<FAST>", "achieved": achieved, "peak": peak,
+            "roofline": {"bound": "hbm", "kernel": "k_wave_trace_persistent", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
                          "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
                          "traffic": prof.get("dram_bytes_per_launch"),

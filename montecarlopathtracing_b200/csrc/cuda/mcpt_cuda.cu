@@ -83,6 +83,7 @@ struct mcpt_ctx {
 	// wavefront path
 	int wave_samples = 0;             // allocated samples per wave
 	DevBuf<float4> od[2], dp[2], cs[2], sample_out;
+	DevBuf<float2> hitrec;
 	DevBuf<uint32_t> qcount, qhead, first_sample;   // qhead[d]: work-fetch cursor of the persistent bounce d (+1 slot for mcpt_trace)
 	int nsm = 148;
 	DevBuf<unsigned long long> counters;   // 0 nodes, 1 tris, 2 live rays (stage path), 3 rays (wave), 4 paths (wave)
@@ -125,6 +126,7 @@ struct mcpt_ctx {
 		WaveDev w{};
 		for (int k = 0; k < 2; ++k) { w.od[k] = od[k].p; w.dp[k] = dp[k].p; w.cs[k] = cs[k].p; }
 		w.sample_out = sample_out.p;
+		w.hitrec = hitrec.p;
 		w.qcount = qcount.p;
 		w.first_sample = first_sample.p;
 		w.rays_traced = counters.p + 3;
@@ -171,6 +173,7 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 		CU(c->cs[k].alloc(n));
 	}
 	CU(c->sample_out.alloc(n));
+	CU(c->hitrec.alloc(n));
 	c->wave_samples = samples;
 	return MCPT_OK;
 }
@@ -200,6 +203,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	const int g = blocks(total, BS);
 	unsigned long long* cnt = c->counters.p;
 	for (int d = 0; d < D; ++d) {
+		bool timed = false;
 		if (c->time_bounces) {
 			if (c->ev_used + 2 > c->ev_pool.size()) {
 				if (c->ev_pool.size() >= 8192) {       // bounded pool: drain (one sync) and reuse
@@ -217,11 +221,23 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 		}
 		if (c->count_fetches)
 			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, true><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
-		else if (trav == MCPT_TRAVERSAL_FAST && !(c->opt_flags & 2))
-			k_wave_bounce_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, c->qhead.p + d);
+		else if (trav == MCPT_TRAVERSAL_FAST && !(c->opt_flags & 2)) {
+			if (c->opt_flags & 8) {        // fused walk + shade in one persistent kernel (the split pipeline measured faster)
+				k_wave_bounce_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, c->qhead.p + d);
+			} else {
+				k_wave_trace_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, c->prm.tmin, c->qhead.p + d);
+				if (c->time_bounces) {      // the timed kernel is the walk; the shader runs after the stop event
+					CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
+					c->ev_used += 2;
+					timed = true;
+				}
+				k_wave_shade<<<std::min(blocks(total, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, d, D, c->prm.seed_mode);
+				++c->launches;
+			}
+		}
 		else
 			MCPT_DISPATCH_TRAVERSAL(trav, (k_wave_bounce<TRAV, false><<<g, BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, cnt)));
-		if (c->time_bounces) {
+		if (c->time_bounces && !timed) {
 			CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
 			c->ev_used += 2;
 		}

@@ -155,6 +155,7 @@ struct WaveDev {
 	float4* dp[2];          // direction.xyz + path id
 	float4* cs[2];          // throughput rgb + LCG state
 	float4* sample_out;     // finished samples, [s * npix + pixel] = (r, g, b, 0)
+	float2* hitrec;         // split pipeline: (t, closest triangle) of queue item i, written by the trace kernel
 	uint32_t* qcount;       // qcount[d] = live paths entering bounce d
 	uint32_t* first_sample; // device-resident global sample index of the wave's first sample
 	unsigned long long* rays_traced;
@@ -430,6 +431,83 @@ struct BounceJob {
 		}
 	}
 };
+
+// ---- split pipeline: the persistent kernel only walks (so its warps never run the divergent shader with a
+// handful of lanes: measured 8 of 32 lanes active there when fused), a second, fully populated kernel shades
+// and compacts.  Costs 8 B written + 40 B re-read per ray of extra HBM traffic, on a kernel that uses 3% of it.
+struct TraceJob {
+	const WaveDev& w;
+	int src;
+	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+		const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i);
+		ray.origin = ld4(o);
+		ray.direction = f4{d.x, d.y, d.z, 0.0f};
+		return true;
+	}
+	__device__ __forceinline__ void finish(unsigned i, const RayRegs&, const HitRegs& h) {
+		__stcs(w.hitrec + i, make_float2(h.t, __int_as_float(h.closest)));
+	}
+};
+
+__global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_trace_persistent(SceneDev sc, WaveDev w, int depth, float tmin, unsigned* head) {
+	const unsigned total = w.qcount[depth];
+	TraceJob job{w, depth & 1};
+	persistent_walk(sc, tmin, total, head, job);
+}
+
+__global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int depth, int max_depth, int seed_mode) {
+	const int src = depth & 1, dst = src ^ 1;
+	const uint32_t total = w.qcount[depth];
+	const unsigned lane = threadIdx.x & 31u;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < total; base += stride) {   // warp-uniform trip count
+		const uint32_t i = base + lane;
+		bool alive = false;
+		RayRegs ray;
+		f4 color{0, 0, 0, 0};
+		uint32_t seed = 0;
+		int path = 0;
+		if (i < total) {
+			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
+			const float2 hr = __ldcs(w.hitrec + i);
+			const float t = hr.x;
+			const int closest = __float_as_int(hr.y);
+			path = __float_as_int(d.w);
+			const int pixel = path % w.npix;
+			ray.origin = ld4(o);
+			ray.direction = f4{d.x, d.y, d.z, __int_as_float(pixel)};
+			color = f4{c.x, c.y, c.z, 0.0f};
+			seed = uint32_t(__float_as_int(c.w));
+			f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
+			uint32_t mat = 0;
+			if (closest >= 0) {
+				const float4* tp = reinterpret_cast<const float4*>(sc.leaves + closest);
+				float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+				nn = f4{q2.w, q3.w, q4.w, 0.0f};
+				mat = uint32_t(__float_as_int(q1.w));
+				ip = ray.origin + t * ray.direction;
+				if (dot3(ray.direction, nn) > 0) nn = -nn;
+			}
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth);
+			if (!alive) {
+				__stcs(w.sample_out + path, make_float4(color.x, color.y, color.z, 0.0f));
+				if (seed_mode == 0) w.seeds[pixel] = seed;
+			}
+		}
+		const unsigned mask = __ballot_sync(0xffffffffu, alive);
+		if (mask) {
+			uint32_t qb = 0;
+			if (lane == 0) qb = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(mask)));
+			qb = __shfl_sync(0xffffffffu, qb, 0);
+			if (alive) {
+				const uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+				__stcs(w.od[dst] + pos, st4(ray.origin));
+				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
+				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
+			}
+		}
+	}
+}
 
 __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_bounce_persistent(SceneDev sc, WaveDev w, int depth, int max_depth, float tmin, int seed_mode,
                                                                 unsigned* head) {
