@@ -20,14 +20,17 @@ constexpr float TWO_PI_F = 6.28318530717958647692f;   // (float)(2*M_PI), shade.
 // normals and edge cross products, black colour channels).  0 / b is a signed zero for every non-zero,
 // non-NaN b, so that case is answered directly and the divider sees 1 / b instead.
 #ifndef MCPT_FDIV_BYPASS
-#define MCPT_FDIV_BYPASS 1   // bit 0: triangle tests (+3% measured); bits 1,2: f4 divisions of the shader (measured: no gain, off)
+#define MCPT_FDIV_BYPASS 3   // bit 0: scalar divisions (triangle tests, +3% measured); bit 1: the shader's f4 divisions (+1%); bit 2: branch on the w lane only (no gain)
 #endif
 __device__ __forceinline__ float fdiv(float a, float b) {
 #if !(MCPT_FDIV_BYPASS & 1)
 	return a / b;
 #endif
 	const bool z = a == 0.0f && fabsf(b) > 0.0f;
-	const float q = (z ? 1.0f : a) / b;
+	// the select is opaque PTX: written in C++ the compiler folds `z ? 0 : (z ? 1 : a) / b` back into a / b
+	float num;
+	asm("{ .reg .pred p; setp.ne.s32 p, %2, 0; selp.f32 %0, 0f3F800000, %1, p; }" : "=f"(num) : "f"(a), "r"(int(z)));
+	const float q = num / b;
 	return z ? __int_as_float((__float_as_int(a) ^ __float_as_int(b)) & int(0x80000000u)) : q;
 }
 
@@ -230,32 +233,23 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 	const MaterialDev mat = load_material(mats, material_id);
 	f4 new_dir{0, 0, 0, 0}, new_org{0, 0, 0, 0};
 	int32_t new_state = 0;
-	switch (mat.type) {
-	case MCPT_DIFFUSE: {                                                      // :114-123
-		new_dir = random_direction(n, seed, cs_table);
+	// Diffuse (:114-123) and both glossy lobes (:124-154) share ONE call site of randomDirection - the expensive
+	// part (three normalisations) - so the lanes of a warp run it together whatever their material; every lane
+	// still draws its random numbers in the reference's order.
+	if (mat.type == MCPT_DIFFUSE || mat.type == MCPT_GLOSSY) {
+		const bool specular = mat.type == MCPT_GLOSSY && (lcg_random(seed) & 1u);
+		f4 axis = n;
+		if (specular) axis = mirror_direction(n, my_dir);
+		do {
+			new_dir = random_direction(axis, seed, cs_table);
+		} while (specular && dot3(new_dir, n) <= 0);
 		new_org = ip + KERNEL_EPSILON * new_dir;
 		new_state = int32_t(state) + 1;
-		color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
+		if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
+		else color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
 		seed_slot = seed;
-		break;
-	}
-	case MCPT_GLOSSY: {                                                       // :124-154
-		if (lcg_random(seed) & 1u) {
-			f4 reflect = mirror_direction(n, my_dir);
-			new_dir = random_direction(reflect, seed, cs_table);
-			while (dot3(new_dir, n) <= 0) new_dir = random_direction(reflect, seed, cs_table);
-			new_org = ip + KERNEL_EPSILON * new_dir;
-			new_state = int32_t(state) + 1;
-			color = color * mat.ka_ks * cr_pow(dot3(new_dir, reflect), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
-		} else {
-			new_dir = random_direction(n, seed, cs_table);
-			new_org = ip + KERNEL_EPSILON * new_dir;
-			new_state = int32_t(state) + 1;
-			color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
-		}
-		seed_slot = seed;
-		break;
-	}
+	} else
+	switch (mat.type) {
 	case MCPT_LIGHT:                                                          // :155-158
 		ray.origin.w = __int_as_float(int(state | MCPT_RAY_TERM_MASK));
 		color = color * mat.ka_ks;
