@@ -142,6 +142,12 @@ int mcpt_get_bounce_time(mcpt_ctx* ctx, double* ms, uint64_t* launches);
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);
 
+/* ---- BVH build on the device.  Replaces BVH::HLBVH<CPU>::build (BVH/hlbvh.cpp:92-200) for
+ * "bvhtype": "hlbvh": host triangles in, 2*ntris-1 host nodes out, memcmp-equal to mcpt_host_build_bvh
+ * (and so to the reference's array).  Needs no context.  Returns the node count or an MCPT_ERR_* code;
+ * *build_ms (optional) receives the device time of the build without the two host<->device copies. */
+int mcpt_build_lbvh(int device, const mcpt_triangle* tris, int ntris, mcpt_bvh_node* nodes_out, float* build_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -21,6 +21,11 @@ int fail(int code, const std::string& msg) {
 	g_err = msg;
 	return code;
 }
+}  // namespace
+namespace mcpt {
+void set_last_error(const std::string& s) { g_err = s; }     // for the other translation units of the library
+}
+namespace {
 
 #define CU(call)                                                                                       \
 	do {                                                                                               \

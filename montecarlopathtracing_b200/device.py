@@ -25,7 +25,7 @@ EXPORTS = [
     "mcpt_reset_accumulation", "mcpt_read_rays", "mcpt_write_rays", "mcpt_read_hits", "mcpt_write_hits",
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
-    "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time",
+    "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
 ]
 
 
@@ -262,3 +262,15 @@ def image_from_sums(sums, width, height):
     img = np.zeros((height, width, 4), np.float32)
     img[..., :3] = (sums[:3] / n).T.reshape(height, width, 3)
     return img
+
+
+def build_lbvh(triangles, device=0, return_ms=False):
+    """HLBVH node array built on the GPU (mcpt_build_lbvh): byte-identical to host.build_bvh(triangles)."""
+    tris = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
+    nodes = np.zeros(max(1, 2 * len(tris) - 1), dtype=T.BVH_NODE)
+    ms = ctypes.c_float(0.0)
+    r = lib().mcpt_build_lbvh(int(device), _vp(tris), len(tris), _vp(nodes), ctypes.byref(ms))
+    if r < 0:
+        raise McptError("mcpt_build_lbvh: %s" % lib().mcpt_last_error().decode())
+    assert r == len(nodes)
+    return (nodes, ms.value) if return_ms else nodes
