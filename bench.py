@@ -47,8 +47,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--depth", type=int, default=16)
-    ap.add_argument("--spp-per-step", type=int, default=8)
-    ap.add_argument("--samples-in-flight", type=int, default=2)
+    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--samples-in-flight", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--microbench-rays", type=int, default=1 << 24,
                     help="rays per set of the intersection microbench (BASELINE configs[1] uses 64 Mi; 0 = skip)")
@@ -61,7 +61,8 @@ def workload_config(a, n):
                            a.width, a.height, a.depth, a.spp_per_step),
             "scene": a.scene, "resolution": [a.width, a.height], "max_depth": a.depth,
             "spp_per_step_per_gpu": a.spp_per_step, "parallelism": "sample-sharded x%d" % n,
-            "l2": "per-step path-state + sample streams (>=400 MB) exceed the 126 MB L2; scene is meant to stay L2-resident"}
+            "samples_in_flight": a.samples_in_flight,
+            "l2": "per-step path-state + sample streams (about 4 GB at 16 samples in flight) exceed the 126 MB L2; scene is meant to stay L2-resident"}
 
 
 # ---------------------------------------------------------------------------- CPU side
