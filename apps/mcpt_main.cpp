@@ -36,6 +36,7 @@ struct State {
 	int spp = 0;             // config "attempt"
 	uint32_t run_seed = 1;
 	bool reference_seeding = true;
+	bool mis = false;        // --mis: NEE + MIS sampling mode (same image, far less variance; needs order-independent seeds)
 	bool host_bvh = false;   // --host-bvh: build the LBVH with the kept host code instead of the device builder
 };
 
@@ -63,7 +64,8 @@ void init(State& s, int ngpus) {
 		p.max_depth = s.cfg.maxdepth;
 		p.max_attempt = s.cfg.attempt;
 		p.device = g;
-		p.seed_mode = (ngpus > 1 || !s.reference_seeding) ? 1 : 0;
+		p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
+		p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
 		p.run_seed = s.run_seed;
 		p.traversal = MCPT_TRAVERSAL_FAST;
 		mcpt_ctx* c = mcpt_create(&p);
@@ -111,7 +113,8 @@ int main(int argc, char** argv) {
 		else if (a == "--batch") batch = std::atoi(next());
 		else if (a == "--order-independent-seeds") s.reference_seeding = false;
 		else if (a == "--host-bvh") s.host_bvh = true;
-		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch --order-independent-seeds --host-bvh)", a.c_str());
+		else if (a == "--mis") s.mis = true;
+		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch --order-independent-seeds --host-bvh --mis)", a.c_str());
 	}
 	if (mcpt_host_load_config(config.c_str(), configid, &s.cfg) < 0) die("config", mcpt_host_last_error());
 	if (s.cfg.testall || s.cfg.testbvh) die("config", "testbvh/testall (BVH quality harness) is out of scope of this build");
@@ -131,7 +134,7 @@ int main(int argc, char** argv) {
 	const size_t npix = size_t(s.cfg.width) * size_t(s.cfg.height);
 	std::vector<float> img(4 * npix, 0.0f);
 	mcpt_stats tot{};
-	if (gpus == 1) {
+	if (gpus == 1 && !s.mis) {
 		if (mcpt_read_history(s.ctx[0], img.data(), nullptr)) die("readback", mcpt_last_error());
 		mcpt_get_stats(s.ctx[0], &tot);
 	} else {

@@ -66,8 +66,12 @@ typedef struct mcpt_params {
 	int samples_in_flight;    /* seed_mode 1: samples per wave of mcpt_render (0 = automatic); mode 0 uses 1 */
 	float tmin;               /* host EPSILON 0.001f (oclbasic.h:193, scenebuild.cpp:125); 0 selects it */
 	int traversal;            /* MCPT_TRAVERSAL_* used by mcpt_render / mcpt_trace (stage calls take their own) */
-	int reserved[6];
+	int sampling;             /* MCPT_SAMPLING_REFERENCE (0): the reference's estimator, bit-exact.  MCPT_SAMPLING_NEE_MIS (1): the
+	                             same image estimated with next-event estimation + MIS (mcpt_mis.cuh); needs seed_mode 1;
+	                             results come from mcpt_read_sums (sum / count), history stays untouched */
+	int reserved[5];
 } mcpt_params;
+enum { MCPT_SAMPLING_REFERENCE = 0, MCPT_SAMPLING_NEE_MIS = 1 };
 
 typedef struct mcpt_stats {
 	uint64_t rays_traced;     /* live rays that entered an intersect stage since create/reset (Mrays/s numerator) */

@@ -10,6 +10,7 @@
 #include "mcpt.h"
 #include "accel_build.hpp"
 #include "mcpt_kernels.cuh"
+#include "mcpt_mis.cuh"
 
 using namespace mcpt;
 
@@ -89,6 +90,22 @@ struct mcpt_ctx {
 	int wave_samples = 0;             // allocated samples per wave
 	DevBuf<float4> od[2], dp[2], cs[2], sample_out;
 	DevBuf<float2> hitrec;
+	// NEE + MIS mode
+	DevBuf<float4> mis_rad, mis_sod, mis_sdp, mis_scon;
+	DevBuf<float> mis_pdf[2], emit_cdf;
+	DevBuf<float2> mis_shit;
+	DevBuf<uint32_t> mis_scount, mis_shead;
+	DevBuf<int32_t> emit_tri;
+	int nemit = 0;
+	float emit_area = 0.0f;
+	MisDev mis() {
+		MisDev m{};
+		m.rad = mis_rad.p; m.pdf[0] = mis_pdf[0].p; m.pdf[1] = mis_pdf[1].p;
+		m.sod = mis_sod.p; m.sdp = mis_sdp.p; m.scon = mis_scon.p; m.shit = mis_shit.p;
+		m.scount = mis_scount.p;
+		m.emit_tri = emit_tri.p; m.emit_cdf = emit_cdf.p; m.nemit = nemit; m.emit_area = emit_area;
+		return m;
+	}
 	DevBuf<uint32_t> qcount, qhead, first_sample;   // qhead[d]: work-fetch cursor of the persistent bounce d (+1 slot for mcpt_trace)
 	int nsm = 148;
 	DevBuf<unsigned long long> counters;   // 0 nodes, 1 tris, 2 live rays (stage path), 3 rays (wave), 4 paths (wave)
@@ -179,6 +196,10 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 	}
 	CU(c->sample_out.alloc(n));
 	CU(c->hitrec.alloc(n));
+	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS) {
+		CU(c->mis_rad.alloc(n)); CU(c->mis_sod.alloc(n)); CU(c->mis_sdp.alloc(n)); CU(c->mis_scon.alloc(n));
+		CU(c->mis_pdf[0].alloc(n)); CU(c->mis_pdf[1].alloc(n)); CU(c->mis_shit.alloc(n));
+	}
 	c->wave_samples = samples;
 	return MCPT_OK;
 }
@@ -253,6 +274,34 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	return MCPT_OK;
 }
 
+// One wave of the NEE + MIS mode: per bounce walk -> shade (chain + emitter sample) -> walk the shadow rays -> add.
+int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
+	const int D = c->prm.max_depth;
+	const long total = long(nsamples) * c->npix;
+	WaveDev w = c->wave();
+	MisDev m = c->mis();
+	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	CU(cudaMemsetAsync(c->qhead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	CU(cudaMemsetAsync(c->mis_scount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	CU(cudaMemsetAsync(c->mis_shead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
+	CU(cudaMemsetAsync(c->mis_rad.p, 0, sizeof(float4) * size_t(total), c->stream));
+	CU(cudaMemsetAsync(c->mis_pdf[0].p, 0, sizeof(float) * size_t(total), c->stream));
+	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
+	const int BS = 128;
+	const int pg = std::min(blocks(total, BS), c->persistent_grid(BS));
+	const int sg = std::min(blocks(total, 256), c->nsm * 8);
+	for (int d = 0; d < D; ++d) {
+		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, w.od[d & 1], w.dp[d & 1], w.hitrec, c->qcount.p + d, c->prm.tmin, c->qhead.p + d);
+		k_wave_shade_mis<<<sg, 256, 0, c->stream>>>(c->scene, w, m, d, D);
+		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, m.sod, m.sdp, m.shit, c->mis_scount.p + d, c->prm.tmin, c->mis_shead.p + d);
+		k_wave_nee_add<<<sg, 256, 0, c->stream>>>(m, d);
+	}
+	k_wave_resolve_mis<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, m, nsamples, D);
+	c->launches += uint64_t(4 * D) + 2;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
 int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal, bool count) {
 	const int trav = c->traversal(traversal);
 	const int BS = c->block;
@@ -306,6 +355,16 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	c->prm = *params;
 	if (c->prm.tmin == 0.0f) c->prm.tmin = 0.001f;
 	if (c->prm.seed_mode == 0) c->prm.samples_in_flight = 1;
+	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE && c->prm.sampling != MCPT_SAMPLING_NEE_MIS) {
+		fail(MCPT_ERR_ARG, "mcpt_create: unknown sampling mode");
+		delete c;
+		return nullptr;
+	}
+	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS && c->prm.seed_mode != 1) {
+		fail(MCPT_ERR_ARG, "mcpt_create: MCPT_SAMPLING_NEE_MIS needs seed_mode 1 (it renders in waves of whole samples)");
+		delete c;
+		return nullptr;
+	}
 	c->npix = params->width * params->height;
 	c->nsm = prop.multiProcessorCount;
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
@@ -316,7 +375,8 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	     c->color.alloc(n) == cudaSuccess && c->hist.alloc(n) == cudaSuccess && c->display.alloc(n) == cudaSuccess &&
 	     c->seeds.alloc(n) == cudaSuccess && c->counts.alloc(n) == cudaSuccess && c->sums_own.alloc(7 * n) == cudaSuccess &&
 	     c->qcount.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->qhead.alloc(size_t(params->max_depth) + 2) == cudaSuccess && c->first_sample.alloc(1) == cudaSuccess &&
-	     c->counters.alloc(8) == cudaSuccess;
+	     c->counters.alloc(8) == cudaSuccess && c->mis_scount.alloc(size_t(params->max_depth) + 2) == cudaSuccess &&
+	     c->mis_shead.alloc(size_t(params->max_depth) + 2) == cudaSuccess;
 	if (ok) {
 		c->sums = c->sums_own.p;
 		ok = cudaMemsetAsync(c->rays.p, 0, sizeof(mcpt_ray) * n, c->stream) == cudaSuccess &&
@@ -347,6 +407,38 @@ int mcpt_synchronize(mcpt_ctx* c) {
 	return MCPT_OK;
 }
 
+// Emitter triangles (material type LIGHT) with an area CDF, for the NEE + MIS mode.
+static int build_emitters(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats) {
+	std::vector<int32_t> list;
+	std::vector<double> area;
+	double total = 0.0;
+	for (int i = 0; i < ntris; ++i) {
+		if (mats[tris[i].material_id].type != MCPT_LIGHT) continue;
+		const mcpt_float4 &a = tris[i].v[0], &b = tris[i].v[1], &d = tris[i].v[2];
+		const double ux = double(b.x) - a.x, uy = double(b.y) - a.y, uz = double(b.z) - a.z;
+		const double vx = double(d.x) - a.x, vy = double(d.y) - a.y, vz = double(d.z) - a.z;
+		const double cx = uy * vz - uz * vy, cy = uz * vx - ux * vz, cz = ux * vy - uy * vx;
+		const double ar = 0.5 * std::sqrt(cx * cx + cy * cy + cz * cz);
+		if (!(ar > 0.0) || !std::isfinite(ar)) continue;
+		list.push_back(i);
+		total += ar;
+		area.push_back(total);
+	}
+	std::vector<float> cdf(list.size());
+	for (size_t k = 0; k < list.size(); ++k) cdf[k] = float(area[k] / total);
+	if (!cdf.empty()) cdf.back() = 1.0f;
+	c->nemit = int(list.size());
+	c->emit_area = float(total);
+	CU(c->emit_tri.alloc(std::max<size_t>(1, list.size())));
+	CU(c->emit_cdf.alloc(std::max<size_t>(1, list.size())));
+	if (!list.empty()) {
+		CU(cudaMemcpyAsync(c->emit_tri.p, list.data(), sizeof(int32_t) * list.size(), cudaMemcpyHostToDevice, c->stream));
+		CU(cudaMemcpyAsync(c->emit_cdf.p, cdf.data(), sizeof(float) * list.size(), cudaMemcpyHostToDevice, c->stream));
+		CU(cudaStreamSynchronize(c->stream));     // the host vectors go out of scope
+	}
+	return MCPT_OK;
+}
+
 int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes) {
 	if (int r = check_ctx(c, false, false)) return r;
@@ -370,7 +462,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
 		CU(cudaStreamSynchronize(c->stream));
 		c->scene.materials = c->mats.p;
-		return MCPT_OK;
+		return build_emitters(c, tris, ntris, mats);
 	}
 	// ---- validate + derive the traversal layout (host side, once per scene)
 	std::vector<DLeaf> dt(ntris);
@@ -529,7 +621,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	c->cache_nodes.assign(nodes, nodes + nnodes);
 	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs, have_q ? d_qnodes : nullptr, qframe};
 	c->have_scene = true;
-	return MCPT_OK;
+	return build_emitters(c, tris, ntris, mats);
 }
 
 int mcpt_set_camera(mcpt_ctx* c, const mcpt_camera* cam) {
@@ -623,6 +715,8 @@ int mcpt_frame(mcpt_ctx* c) {
 int mcpt_render_async(mcpt_ctx* c, int spp) {
 	if (int r = check_ctx(c, true, true)) return r;
 	if (spp < 0) return fail(MCPT_ERR_ARG, "mcpt_render: negative spp");
+	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS && (c->force_reference || c->scene.root_is_leaf))
+		return fail(MCPT_ERR_STATE, "mcpt_render: the NEE + MIS mode needs the fast walk, which this scene cannot use (single triangle or boxes not nested)");
 	int S = c->prm.seed_mode == 0 ? 1 : c->prm.samples_in_flight;
 	if (S <= 0) {
 		// automatic: about 32 Mi paths in flight (120 B each), never more than a quarter of the free memory.  Large
@@ -640,7 +734,7 @@ int mcpt_render_async(mcpt_ctx* c, int spp) {
 	if (int r = ensure_wave(c, S)) return r;
 	for (int done = 0; done < spp;) {
 		int s = spp - done < S ? spp - done : S;
-		if (int r = enqueue_wave(c, s)) return r;
+		if (int r = (c->prm.sampling == MCPT_SAMPLING_NEE_MIS ? enqueue_wave_mis(c, s) : enqueue_wave(c, s))) return r;
 		done += s;
 	}
 	return MCPT_OK;

@@ -221,7 +221,8 @@ __device__ __forceinline__ MaterialDev load_material(const mcpt_material* __rest
 
 __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
                                           RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
-                                          uint32_t& seed_slot, int max_depth) {
+                                          uint32_t& seed_slot, int max_depth, bool* diffuse_lobe = nullptr) {
+	if (diffuse_lobe) *diffuse_lobe = false;
 	const uint32_t state = uint32_t(__float_as_int(ray.origin.w));
 	if (hit_t >= FLT_MAX) {                                                   // :92-96
 		color = f4{0, 0, 0, 0};
@@ -247,6 +248,7 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		new_state = int32_t(state) + 1;
 		if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
 		else color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
+		if (diffuse_lobe) *diffuse_lobe = !specular;
 		seed_slot = seed;
 	} else
 	switch (mat.type) {
@@ -288,6 +290,21 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 	ray.origin = f4{new_org.x, new_org.y, new_org.z, __int_as_float(new_state)};
 	ray.direction = f4{new_dir.x, new_dir.y, new_dir.z, pixel_w};
 	return alive;
+}
+
+// ------------------------------------------------------------------ NEE + MIS sampling mode (not in the reference)
+// Solid-angle density of randomDirection (shade.cl:40-59) about `normal`, as a function of c = cos(theta):
+// it draws u ~ U[0,1), phi ~ U[0, 2 pi) and returns the direction of (sqrt(u) cos phi, sqrt(u) sin phi, 1 - u), so
+// c = (1-u)/sqrt(D), D = 1 - u + u^2, and p = |du/dc| / (2 pi) = D^(3/2) / (pi (1 + u)); inverting c(u) gives
+// 1 - u = 2c / (c + sqrt(4 - 3 c^2)) (the cancellation-free form of SURVEY's expression).  The reference's u and
+// phi live on 2^15-point grids; the continuous density is their limit (relative difference ~1e-4).
+__device__ __forceinline__ float random_direction_pdf(float c) {
+	if (!(c > 0.0f)) return 0.0f;
+	c = fminf(c, 1.0f);
+	const float v = 2.0f * c / (c + sqrtf(4.0f - 3.0f * c * c));
+	const float u = 1.0f - v;
+	const float D = 1.0f - u + u * u;
+	return D * sqrtf(D) / (3.14159265358979f * (1.0f + u));
 }
 
 // ------------------------------------------------------------------ K4 (history.cl:3-28)

@@ -17,6 +17,7 @@ _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 TRAVERSAL_REFERENCE, TRAVERSAL_FAST, TRAVERSAL_CANONICAL, TRAVERSAL_WIDE8 = 0, 1, 2, 3
+SAMPLING_REFERENCE, SAMPLING_NEE_MIS = 0, 1
 
 EXPORTS = [
     "mcpt_last_error", "mcpt_abi_version", "mcpt_create", "mcpt_destroy", "mcpt_stream", "mcpt_synchronize",
@@ -33,7 +34,7 @@ class Params(ctypes.Structure):
     _fields_ = [("width", ctypes.c_int), ("height", ctypes.c_int), ("max_depth", ctypes.c_int),
                 ("max_attempt", ctypes.c_int), ("device", ctypes.c_int), ("seed_mode", ctypes.c_int),
                 ("run_seed", ctypes.c_uint32), ("samples_in_flight", ctypes.c_int), ("tmin", ctypes.c_float),
-                ("traversal", ctypes.c_int), ("reserved", ctypes.c_int * 6)]
+                ("traversal", ctypes.c_int), ("sampling", ctypes.c_int), ("reserved", ctypes.c_int * 5)]
 
 
 class Stats(ctypes.Structure):
@@ -81,10 +82,10 @@ class Context:
     """One device context = the reference's OpenCLApp state (OpenCLApp.cpp:17-33) for one scene."""
 
     def __init__(self, width, height, max_depth, max_attempt, device=0, seed_mode=0, run_seed=1, samples_in_flight=0,
-                 tmin=0.001, traversal=TRAVERSAL_FAST):
+                 tmin=0.001, traversal=TRAVERSAL_FAST, sampling=0):
         self.width, self.height, self.max_depth, self.max_attempt = width, height, max_depth, max_attempt
         self.npix = width * height
-        p = Params(width, height, max_depth, max_attempt, device, seed_mode, run_seed, samples_in_flight, tmin, traversal)
+        p = Params(width, height, max_depth, max_attempt, device, seed_mode, run_seed, samples_in_flight, tmin, traversal, sampling)
         self._L = lib()
         self._h = self._L.mcpt_create(ctypes.byref(p))
         if not self._h:
