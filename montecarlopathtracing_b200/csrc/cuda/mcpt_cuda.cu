@@ -547,6 +547,19 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	std::vector<DNode> fast;
 	if (!root_leaf) build_sah_bvh2(dt.data(), ntris, fast);
 	else fast.assign(1, DNode{});
+	// the fast walk pushes at most one entry per level and does not check its stack: verify the depth here
+	int fast_depth = 0;
+	if (!root_leaf) {
+		std::vector<std::pair<int, int>> todo{{0, 1}};
+		while (!todo.empty()) {
+			auto [node, d] = todo.back();
+			todo.pop_back();
+			fast_depth = std::max(fast_depth, d);
+			if (fast[size_t(node)].left >= 0) todo.push_back({fast[size_t(node)].left, d + 1});
+			if (fast[size_t(node)].right >= 0) todo.push_back({fast[size_t(node)].right, d + 1});
+		}
+	}
+	const bool fast_too_deep = fast_depth > STACK_SIZE;
 	std::vector<WNode> wide;
 	std::vector<DLeaf> wide_leaves;
 	build_wide_bvh8(fast, dt.data(), ntris, wide, wide_leaves);
@@ -598,7 +611,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	float max_abs = 0.0f;
 	for (float v : {nodes[0].bbmin.x, nodes[0].bbmin.y, nodes[0].bbmin.z, nodes[0].bbmax.x, nodes[0].bbmax.y, nodes[0].bbmax.z})
 		max_abs = std::max(max_abs, std::fabs(v));
-	if (!(max_abs < 1e30f) || (MCPT_QNODES && !have_q && !root_leaf)) c->force_reference = true;   // no grid frame: degenerate scene
+	if (!(max_abs < 1e30f) || fast_too_deep || (MCPT_QNODES && !have_q && !root_leaf)) c->force_reference = true;   // no grid frame: degenerate scene
 	// Keep the walk's working set resident in L2: the per-bounce ray / path-state streams (hundreds of MB)
 	// otherwise evict it, and every evicted node costs a whole warp a DRAM round trip (ncu: 20% L2 misses,
 	// 0.6 DRAM node fetches per ray).  Measured on B200: no gain (-1%), so it is opt-in: MCPT_OPT bit 2.

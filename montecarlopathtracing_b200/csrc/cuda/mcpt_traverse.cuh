@@ -341,7 +341,7 @@ constexpr int LEAF_FLAG = int(0x80000000);
 #define MCPT_LEAF_LINKS 1 // fast nodes store leaf links as LEAF_FLAG | triangle (no decode in the loop)
 #endif
 #ifndef MCPT_POSTPONE_LEAF
-#define MCPT_POSTPONE_LEAF 1
+#define MCPT_POSTPONE_LEAF 0   // 1: keep descending after the first leaf (Aila-Laine "postponed leaf"): measured -1.7% on the loop, -6% coherent
 #endif
 
 struct CandList {
@@ -558,7 +558,7 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		if (hitL && hitR) {
 			const bool swap = loR < loL;
 			const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
-			if (sp < STACK_SIZE) w.stack[sp++] = farc; else w.cl.overflow = true;
+			w.stack[sp++] = farc;      // cannot overflow: mcpt_upload_scene checks the depth of the fast tree against STACK_SIZE
 			cur = nearc;
 		} else if (hitL) cur = cl_;
 		else if (hitR) cur = cr_;
