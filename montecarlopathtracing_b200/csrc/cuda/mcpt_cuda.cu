@@ -161,6 +161,10 @@ struct mcpt_ctx {
 		return w;
 	}
 	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
+	// host copies kept for the lazily built 8-wide layout (MCPT_TRAVERSAL_WIDE8, experimental)
+	std::vector<DNode> host_fast;
+	std::vector<DLeaf> host_leaves;
+	bool have_wide = false;
 	int persistent_grid(int bs) const { return nsm * (MCPT_MIN_BLOCKS * 128 / bs); }
 };
 
@@ -217,6 +221,8 @@ int reset_accumulation(mcpt_ctx* c) {
 }
 
 // One wave of the fused pipeline: nsamples consecutive samples of every pixel.
+int ensure_wide(mcpt_ctx* c);
+
 int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	const int D = c->prm.max_depth;
 	const long total = long(nsamples) * c->npix;
@@ -225,6 +231,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	CU(cudaMemsetAsync(c->qhead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int trav = c->traversal(c->prm.traversal);
+	if (trav == MCPT_TRAVERSAL_WIDE8) if (int r = ensure_wide(c)) return r;
 	const int BS = c->block;
 	const int g = blocks(total, BS);
 	unsigned long long* cnt = c->counters.p;
@@ -274,6 +281,24 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	return MCPT_OK;
 }
 
+int ensure_wide(mcpt_ctx* c) {
+	if (c->have_wide) return MCPT_OK;
+	std::vector<WNode> wide;
+	std::vector<DLeaf> wide_leaves;
+	build_wide_bvh8(c->host_fast, c->host_leaves.data(), int(c->host_leaves.size()), wide, wide_leaves);
+	CU(cudaStreamSynchronize(c->stream));
+	CU(c->wnodes.alloc(std::max<size_t>(1, wide.size())));
+	CU(c->wleaves.alloc(std::max<size_t>(1, wide_leaves.size())));
+	if (!wide.empty()) CU(cudaMemcpyAsync(c->wnodes.p, wide.data(), sizeof(WNode) * wide.size(), cudaMemcpyHostToDevice, c->stream));
+	if (!wide_leaves.empty())
+		CU(cudaMemcpyAsync(c->wleaves.p, wide_leaves.data(), sizeof(DLeaf) * wide_leaves.size(), cudaMemcpyHostToDevice, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	c->scene.wnodes = c->wnodes.p;
+	c->scene.wleaves = c->wleaves.p;
+	c->have_wide = true;
+	return MCPT_OK;
+}
+
 // One wave of the NEE + MIS mode: per bounce walk -> shade (chain + emitter sample) -> walk the shadow rays -> add.
 int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 	const int D = c->prm.max_depth;
@@ -304,6 +329,7 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 
 int launch_intersect(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal, bool count) {
 	const int trav = c->traversal(traversal);
+	if (trav == MCPT_TRAVERSAL_WIDE8) if (int r = ensure_wide(c)) return r;
 	const int BS = c->block;
 	const int g = blocks(n, BS);
 	unsigned long long* cnt = c->counters.p;
@@ -560,15 +586,11 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		}
 	}
 	const bool fast_too_deep = fast_depth > STACK_SIZE;
-	std::vector<WNode> wide;
-	std::vector<DLeaf> wide_leaves;
-	build_wide_bvh8(fast, dt.data(), ntris, wide, wide_leaves);
+	// the experimental 8-wide layout is derived on first use (ensure_wide), not on every upload
+	c->host_fast = fast;
+	c->host_leaves = dt;
+	c->have_wide = false;
 	CU(cudaStreamSynchronize(c->stream));
-	CU(c->wnodes.alloc(wide.size()));
-	CU(c->wleaves.alloc(std::max<size_t>(1, wide_leaves.size())));
-	CU(cudaMemcpyAsync(c->wnodes.p, wide.data(), sizeof(WNode) * wide.size(), cudaMemcpyHostToDevice, c->stream));
-	if (!wide_leaves.empty())
-		CU(cudaMemcpyAsync(c->wleaves.p, wide_leaves.data(), sizeof(DLeaf) * wide_leaves.size(), cudaMemcpyHostToDevice, c->stream));
 	std::vector<QNode> qn;
 	QFrame qframe{};
 #if MCPT_QNODES
@@ -679,6 +701,7 @@ int mcpt_intersect(mcpt_ctx* c, int traversal) {
 	const int trav = c->traversal(traversal);
 	const int g = blocks(c->npix, 128);
 	if (trav < 0 || trav > 3) return fail(MCPT_ERR_ARG, "unknown traversal");
+	if (trav == MCPT_TRAVERSAL_WIDE8) if (int r = ensure_wide(c)) return r;
 	MCPT_DISPATCH_TRAVERSAL(trav, (k_intersect<TRAV, true><<<g, 128, 0, c->stream>>>(c->scene, c->rays.p, c->npix, c->prm.tmin, c->hits.p, c->closest.p, c->counters.p)));
 	++c->launches;
 	CU(cudaGetLastError());
