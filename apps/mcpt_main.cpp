@@ -50,9 +50,13 @@ void init(State& s, int ngpus) {
 	if (mcpt_host_load_object(s.cfg.directory, s.cfg.objname, 1, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
 		die("loadObject", mcpt_host_last_error());
 	s.nodes.resize(size_t(2 * s.ntris - 1));
-	// "hlbvh": built on GPU 0 (same bytes as the host build, ~100x faster); the treelet variants post-process on the host
-	if (!s.host_bvh && std::string(s.cfg.bvhtype) == "hlbvh") {
+	// built on GPU 0 (same bytes as the host build, ~100x faster); --host-bvh keeps the host code
+	const std::string bvhtype = s.cfg.bvhtype;
+	if (!s.host_bvh && (bvhtype == "hlbvh" || bvhtype == "treelet" || bvhtype == "treeletGPU")) {
 		if (mcpt_build_lbvh(0, s.tris, s.ntris, s.nodes.data(), nullptr) < 0) die("BVH (device)", mcpt_last_error());
+		// both treelet spellings: the device optimiser, whose output equals TreeletBVH<CPU>'s byte for byte
+		if (bvhtype != "hlbvh" && mcpt_optimize_treelet(0, s.nodes.data(), int(s.nodes.size()), s.nodes.data(), nullptr) < 0)
+			die("treelet (device)", mcpt_last_error());
 	} else if (mcpt_host_build_bvh(s.tris, s.ntris, s.cfg.bvhtype, s.nodes.data()) < 0) die("BVH", mcpt_host_last_error());
 	if (!s.cfg.has_camera) die("config", "no camera");
 	if (s.cfg.res_x != s.cfg.width || s.cfg.res_y != s.cfg.height)

@@ -152,6 +152,13 @@ int mcpt_reset_stats(mcpt_ctx* ctx);
  * *build_ms (optional) receives the device time of the build without the two host<->device copies. */
 int mcpt_build_lbvh(int device, const mcpt_triangle* tris, int ntris, mcpt_bvh_node* nodes_out, float* build_ms);
 
+/* ---- Treelet restructuring on the device.  Replaces BVH::TreeletBVH<CPU> (BVH/treeletBVH.cpp:30-365,
+ * "bvhtype": "treelet") and stands in for the reference's racy TreeletBVH<GPU> (kernels/treeletBVH.cl:230-531,
+ * "bvhtype": "treeletGPU"): host nodes in (any 2N-1 array in the reference layout, e.g. from mcpt_build_lbvh),
+ * host nodes out, memcmp-equal to mcpt_host_treelet.  Fails with MCPT_ERR_STATE where the reference's SAH recursion
+ * would not terminate (same condition and message as the host optimiser).  nodes_out may alias nodes_in. */
+int mcpt_optimize_treelet(int device, const mcpt_bvh_node* nodes_in, int nnodes, mcpt_bvh_node* nodes_out, float* build_ms);
+
 #ifdef __cplusplus
 }
 #endif

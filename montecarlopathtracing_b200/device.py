@@ -27,6 +27,7 @@ EXPORTS = [
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
+    "mcpt_optimize_treelet",
 ]
 
 
@@ -275,3 +276,15 @@ def build_lbvh(triangles, device=0, return_ms=False):
         raise McptError("mcpt_build_lbvh: %s" % lib().mcpt_last_error().decode())
     assert r == len(nodes)
     return (nodes, ms.value) if return_ms else nodes
+
+
+def optimize_treelet(nodes, device=0, return_ms=False):
+    """Treelet-restructured node array from the GPU (mcpt_optimize_treelet): byte-identical to host.treelet(nodes)."""
+    src = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    out = np.zeros_like(src)
+    ms = ctypes.c_float(0.0)
+    r = lib().mcpt_optimize_treelet(int(device), _vp(src), len(src), _vp(out), ctypes.byref(ms))
+    if r < 0:
+        raise McptError("mcpt_optimize_treelet: %s" % lib().mcpt_last_error().decode())
+    assert r == len(out)
+    return (out, ms.value) if return_ms else out
