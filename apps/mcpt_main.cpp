@@ -47,7 +47,7 @@ struct State {
 
 void init(State& s, int ngpus) {
 	if (!s.cfg.opencl) die("config", "Not Implemented");            // raygeneration.cpp:36-38 throws the same
-	if (mcpt_host_load_object(s.cfg.directory, s.cfg.objname, 1, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
+	if (mcpt_host_load_object_mt(s.cfg.directory, s.cfg.objname, 1, 0, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
 		die("loadObject", mcpt_host_last_error());
 	s.nodes.resize(size_t(2 * s.ntris - 1));
 	// built on GPU 0 (same bytes as the host build, ~100x faster); --host-bvh keeps the host code

@@ -342,6 +342,12 @@ def run_b200(a):
         peak = float(peaks["hbm_gbs"]) if peaks and "hbm_gbs" in peaks else 6650.0
         prof = read_json(os.path.join(ROOT, "profiles", "traffic.json")) or {}
         achieved = bytes_per_ray * (rays / world) / (bounce_ms_max * 1e-3) / 1e9 if bounce_ms_max > 0 else None
+        # the walk's bytes come out of L1/L2, not HBM: measure the L2 streaming-read ceiling next to it (32 MiB buffer)
+        try:
+            l2_peak = device.measure_read_bandwidth(32 << 20, iters=40, device=local)
+        except Exception as e:      # measurement aid only
+            l2_peak = None
+            sys.stderr.write("l2 probe failed: %s\n" % e)
         out = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -359,7 +365,11 @@ def run_b200(a):
                          "tris_per_ray": tris_per_ray,
                          "kernel_ms_per_step": bounce_ms_max / a.steps, "kernel_launches": int(bounce_launches),
                          "kernel_share_of_step": bounce_ms_max / ms_max,
-                         "note": "algorithmic bytes are served mostly by L1/L2 (scene is L2-resident)"},
+                         "l2": {"peak": l2_peak, "unit": "GB/s", "frac": (achieved / l2_peak) if (achieved and l2_peak) else None,
+                                "how": "streaming ld.global.cg read of a 32 MiB buffer, 148x8 blocks, best of 5"},
+                         "note": "algorithmic bytes are served mostly by L1/L2 (scene is L2-resident): frac is against "
+                                 "what HBM could feed; l2.frac is the same bytes against the measured L2 read ceiling; "
+                                 "the binding unit per ncu is the L1 data pipe (profiles/r1h_trace_shade_ncu_full.txt)"},
             "clocks": clk,
         }
         if world == 1 and a.microbench_rays > 0:

@@ -24,6 +24,7 @@
 #ifndef MCPT_H
 #define MCPT_H
 
+#include <stddef.h>
 #include "mcpt_types.h"
 
 #ifdef __cplusplus
@@ -142,6 +143,10 @@ int mcpt_trace_count(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, int traversa
  *                  time and launch count since the last call are returned by mcpt_get_bounce_time. */
 int mcpt_set_profiling(mcpt_ctx* ctx, int count_fetches, int time_bounces);
 int mcpt_get_bounce_time(mcpt_ctx* ctx, double* ms, uint64_t* launches);
+
+/* Streaming-read bandwidth (GB/s, best of 5) of a scratch buffer of `bytes` read `iters` times on `device`:
+ * 32 MiB measures the L2 ceiling the walk's node fetches live under, several GiB the HBM ceiling.  Needs no context. */
+int mcpt_measure_read_bandwidth(int device, size_t bytes, int iters, float* gb_per_s);
 
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);

@@ -45,6 +45,11 @@ void mcpt_host_free(void* p);
 int mcpt_host_load_object(const char* directory, const char* objname, int with_normals,
                           mcpt_triangle** tris, int* ntris, mcpt_material** mats, int* nmats,
                           int** material_ids);
+/* the same arrays, byte for byte, parsed by `threads` host threads (0 = all, 1 = the serial loader).
+ * tinyobj (tiny_obj_loader.h:2063) and the loader above are single-threaded; 16 MB of OBJ: 0.5 s -> see README. */
+int mcpt_host_load_object_mt(const char* directory, const char* objname, int with_normals, int threads,
+                             mcpt_triangle** tris, int* ntris, mcpt_material** mats, int* nmats,
+                             int** material_ids);
 /* out_nodes must hold 2*n-1 nodes; returns the node count. bvhtype: "hlbvh" | "treelet" | "treeletGPU" */
 int mcpt_host_build_bvh(const mcpt_triangle* tris, int n, const char* bvhtype, mcpt_bvh_node* out_nodes);
 int mcpt_host_treelet(const mcpt_bvh_node* nodes_in, int nn, mcpt_bvh_node* out_nodes);

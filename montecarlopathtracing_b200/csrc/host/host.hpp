@@ -69,6 +69,8 @@ struct Scene {
 };
 // with_normals=false leaves Triangle::normal/material_id zero exactly like loadObject() does.
 Scene load_object(const std::string& directory, const std::string& objname, bool with_normals = true);
+// Same result, parsed by `threads` threads (0 = all hardware threads, 1 = the serial loader above).
+Scene load_object_parallel(const std::string& directory, const std::string& objname, bool with_normals, int threads);
 
 // ------------------------------------------------------------------ BVH
 // LBVH (BVH/hlbvh.cpp:92-200): 30-bit Morton of AABB centroids, stable sort, split at the

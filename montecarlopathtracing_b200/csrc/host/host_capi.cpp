@@ -44,6 +44,20 @@ int mcpt_host_load_object(const char* directory, const char* objname, int with_n
 	});
 }
 
+int mcpt_host_load_object_mt(const char* directory, const char* objname, int with_normals, int threads,
+                             mcpt_triangle** tris, int* ntris, mcpt_material** mats, int* nmats,
+                             int** material_ids) {
+	return guarded([&] {
+		Scene s = load_object_parallel(directory, objname, with_normals != 0, threads);
+		*ntris = int(s.triangles.size());
+		*nmats = int(s.materials.size());
+		*tris = dup(s.triangles);
+		*mats = dup(s.materials);
+		*material_ids = dup(s.material_ids);
+		return 0;
+	});
+}
+
 int mcpt_host_build_bvh(const mcpt_triangle* tris, int n, const char* bvhtype, mcpt_bvh_node* out_nodes) {
 	return guarded([&] {
 		std::vector<mcpt_triangle> t(tris, tris + n);

@@ -12,11 +12,17 @@
 //       Ni != 1 -> TRANSPARENT;  Ka > 0 -> LIGHT;  Ns != 1 -> GLOSSY;  else DIFFUSE;
 //   * per-triangle geometric normal + material id as the SceneCL constructor adds them
 //     (scenebuild.cpp:58-62), using the 4-lane host float math of oclbasic.h:117-146.
+#include <algorithm>
 #include <cmath>
+#include <cstdint>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <limits>
+#include <thread>
+#ifdef __linux__
+#include <sched.h>
+#endif
 
 #include "host.hpp"
 
@@ -129,10 +135,10 @@ bool inside_tri(const float vx[3], const float vy[3], float tx, float ty) {
 }
 
 // Ear clipping with tinyobj's exact decision sequence; emits vertex-index triples.
-void triangulate_face(const std::vector<int>& face, const std::vector<float>& v, std::vector<int>& out) {
+// `v`/`nv`: the vertex floats read SO FAR (a face may name a vertex that only appears later in the file).
+void triangulate_face(const std::vector<int>& face, const float* v, size_t nv, std::vector<int>& out) {
 	size_t n = face.size();
 	if (n < 3) return;
-	const size_t nv = v.size();
 	auto ok = [&](int vi, size_t off) { return size_t(vi) * 3 + off < nv; };
 	// projection axes: drop the dominant axis of the first corner with a non-zero cross product
 	size_t ax0 = 1, ax1 = 2;
@@ -231,7 +237,7 @@ Scene load_object(const std::string& directory, const std::string& objname, bool
 				p += std::strcspn(p, " \t");    // skip /vt/vn
 			}
 			tri_idx.clear();
-			triangulate_face(face, verts, tri_idx);
+			triangulate_face(face, verts.data(), verts.size(), tri_idx);
 			for (size_t k = 0; k + 2 < tri_idx.size() + 0 && k < tri_idx.size(); k += 3) {
 				mcpt_triangle tr{};
 				for (int c = 0; c < 3; ++c) {
@@ -282,6 +288,241 @@ Scene load_object(const std::string& directory, const std::string& objname, bool
 			tr.nx = n.x / s; tr.ny = n.y / s; tr.nz = n.z / s;
 			tr.material_id = sc.material_ids[i];
 		}
+	}
+	return sc;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Parallel loader: same bytes as load_object above, which stays the pinned definition.
+// The file is read once and cut at line ends into one chunk per thread.  Pass 1 (parallel) turns each chunk
+// into vertex floats, raw face indices and the few state-changing lines (usemtl / mtllib) with their position;
+// a short serial pass replays those state changes in file order (material table, current material) and turns
+// per-chunk vertex counts into offsets; pass 2 (parallel) resolves indices against "vertices read so far",
+// ear-clips with the same routine and writes triangles, material ids and normals in place.
+namespace {
+
+struct ChunkEvent {
+	size_t face;              // number of faces of this chunk read before the line
+	bool is_lib;              // mtllib (true) or usemtl (false)
+	std::string arg;
+};
+struct Chunk {
+	const char* begin = nullptr;
+	const char* end = nullptr;
+	std::vector<float> verts;
+	std::vector<long> raw;            // face indices as written (1-based, negative = relative)
+	std::vector<uint32_t> face_len;
+	std::vector<uint32_t> face_nv;    // vertices of THIS chunk read before the face
+	std::vector<ChunkEvent> events;
+	// after the serial pass
+	size_t vert_base = 0;             // vertices (not floats) in earlier chunks
+	std::vector<std::pair<size_t, int>> mat_runs;   // (first face, material) in face order
+	std::vector<mcpt_triangle> tris;
+	std::vector<int> tri_mat;
+	std::string error;
+};
+
+// one line [b, e) without its terminator; p advances past \n, \r\n or \r
+inline bool next_line(const char*& p, const char* end, const char*& b, const char*& e) {
+	if (p >= end) return false;
+	b = p;
+	while (p < end && *p != '\n' && *p != '\r') ++p;
+	e = p;
+	if (p < end) {
+		if (*p == '\r' && p + 1 < end && p[1] == '\n') p += 2;
+		else ++p;
+	}
+	return true;
+}
+
+void parse_chunk(Chunk& c) {
+	const char* p = c.begin;
+	const char *b, *e;
+	std::string line;
+	while (next_line(p, c.end, b, e)) {
+		while (e > b && is_space(e[-1])) --e;
+		if (e == b) continue;
+		line.assign(b, e);
+		const char* t = line.c_str();
+		t += std::strspn(t, " \t");
+		if (*t == '\0' || *t == '#') continue;
+		if (t[0] == 'v' && is_space(t[1])) {
+			const char* q = t + 2;
+			for (int i = 0; i < 3; ++i) c.verts.push_back(parse_float(q));
+		} else if (t[0] == 'f' && is_space(t[1])) {
+			const char* q = t + 2;
+			uint32_t len = 0;
+			for (;;) {
+				q += std::strspn(q, " \t");
+				if (*q == '\0') break;
+				char* ep = nullptr;
+				long i = std::strtol(q, &ep, 10);
+				if (ep == q) break;
+				c.raw.push_back(i);
+				++len;
+				q = ep;
+				q += std::strcspn(q, " \t");
+			}
+			c.face_len.push_back(len);
+			c.face_nv.push_back(uint32_t(c.verts.size() / 3));
+		} else if (std::strncmp(t, "usemtl", 6) == 0 && is_space(t[6])) {
+			c.events.push_back({c.face_len.size(), false, std::string(t + 7)});
+		} else if (std::strncmp(t, "mtllib", 6) == 0 && is_space(t[6])) {
+			c.events.push_back({c.face_len.size(), true, std::string(t + 7)});
+		}
+	}
+}
+
+void emit_chunk(Chunk& c, const std::vector<float>& verts) {
+	std::vector<int> face, tri_idx;
+	size_t r = 0, run = 0;
+	int cur_mat = c.mat_runs.empty() ? -1 : c.mat_runs[0].second;
+	for (size_t f = 0; f < c.face_len.size(); ++f) {
+		while (run + 1 < c.mat_runs.size() && c.mat_runs[run + 1].first <= f) ++run;
+		if (!c.mat_runs.empty()) cur_mat = c.mat_runs[run].second;
+		const int nverts_now = int(c.vert_base + c.face_nv[f]);
+		const size_t nfloats_now = size_t(nverts_now) * 3;
+		face.clear();
+		for (uint32_t k = 0; k < c.face_len[f]; ++k) {
+			const long i = c.raw[r++];
+			face.push_back(i > 0 ? int(i - 1) : (i < 0 ? nverts_now + int(i) : 0));
+		}
+		tri_idx.clear();
+		triangulate_face(face, verts.data(), nfloats_now, tri_idx);
+		for (size_t k = 0; k + 2 < tri_idx.size(); k += 3) {
+			mcpt_triangle tr{};
+			for (int v = 0; v < 3; ++v) {
+				size_t b = size_t(tri_idx[k + v]) * 3;
+				if (b + 2 >= nfloats_now) { c.error = "obj: vertex index out of range"; return; }
+				tr.v[v] = mcpt_float4{verts[b], verts[b + 1], verts[b + 2], 0.0f};
+			}
+			c.tris.push_back(tr);
+			c.tri_mat.push_back(cur_mat);
+		}
+	}
+}
+
+template <class F>
+void run_threads(size_t n, F&& fn) {
+	std::vector<std::thread> th;
+	for (size_t i = 1; i < n; ++i) th.emplace_back([&fn, i] { fn(i); });
+	fn(0);
+	for (auto& t : th) t.join();
+}
+
+}  // namespace
+
+Scene load_object_parallel(const std::string& directory, const std::string& objname, bool with_normals, int threads) {
+	if (threads <= 0) {
+		threads = int(std::thread::hardware_concurrency());
+#ifdef __linux__
+		cpu_set_t set;                                    // a container may be allowed fewer cores than the machine has
+		if (sched_getaffinity(0, sizeof(set), &set) == 0) threads = std::min(threads, std::max(1, CPU_COUNT(&set)));
+#endif
+		threads = std::min(threads, 32);
+	}
+	if (threads <= 1) return load_object(directory, objname, with_normals);
+	std::string data;
+	{
+		std::ifstream in(directory + objname, std::ios::binary);
+		if (!in) throw std::runtime_error("cannot open " + directory + objname);
+		in.seekg(0, std::ios::end);
+		const std::streamoff sz = in.tellg();
+		in.seekg(0, std::ios::beg);
+		data.resize(size_t(sz > 0 ? sz : 0));
+		if (!data.empty()) in.read(&data[0], std::streamsize(data.size()));
+	}
+	const char* base = data.data();
+	const char* end = base + data.size();
+	size_t nchunks = std::min<size_t>(size_t(threads), std::max<size_t>(1, data.size() / 65536));
+	std::vector<Chunk> chunks(nchunks);
+	{
+		const char* p = base;
+		for (size_t i = 0; i < nchunks; ++i) {
+			chunks[i].begin = p;
+			const char* target = (i + 1 == nchunks) ? end : base + data.size() * (i + 1) / nchunks;
+			if (target < p) target = p;
+			const char *b, *e;
+			const char* q = target;
+			if (q < end) next_line(q, end, b, e);      // finish the line `target` falls into
+			chunks[i].end = p = q;
+		}
+		chunks.back().end = end;
+	}
+	run_threads(nchunks, [&](size_t i) { parse_chunk(chunks[i]); });
+
+	// ---- serial replay of the state-changing lines, vertex offsets
+	Scene sc;
+	std::vector<MtlRecord> mtl;
+	std::map<std::string, int> mtl_index;
+	int cur_mat = -1;
+	size_t nverts = 0;
+	for (Chunk& c : chunks) {
+		c.vert_base = nverts;
+		nverts += c.verts.size() / 3;
+		c.mat_runs.push_back({0, cur_mat});
+		for (const ChunkEvent& ev : c.events) {
+			if (!ev.is_lib) {
+				auto it = mtl_index.find(ev.arg);
+				cur_mat = it == mtl_index.end() ? -1 : it->second;
+				c.mat_runs.push_back({ev.face, cur_mat});
+				continue;
+			}
+			size_t pos = 0;
+			while (pos < ev.arg.size()) {     // first file that loads wins (tiny_obj_loader.h:2346-2375)
+				size_t sp = ev.arg.find(' ', pos);
+				std::string fn = ev.arg.substr(pos, sp == std::string::npos ? std::string::npos : sp - pos);
+				pos = sp == std::string::npos ? ev.arg.size() : sp + 1;
+				if (fn.empty()) continue;
+				auto recs = load_mtl(directory + fn);
+				if (recs.empty()) continue;
+				for (auto& r : recs) {
+					mtl_index.emplace(r.name, int(mtl.size()));
+					mtl.push_back(r);
+				}
+				break;
+			}
+		}
+	}
+	std::vector<float> verts(nverts * 3);
+	run_threads(nchunks, [&](size_t i) {
+		if (!chunks[i].verts.empty())
+			std::memcpy(verts.data() + chunks[i].vert_base * 3, chunks[i].verts.data(), chunks[i].verts.size() * sizeof(float));
+	});
+	run_threads(nchunks, [&](size_t i) { emit_chunk(chunks[i], verts); });
+	size_t ntris = 0;
+	std::vector<size_t> tri_base(nchunks);
+	for (size_t i = 0; i < nchunks; ++i) {
+		// the serial loader stops at the first bad face; everything before it is irrelevant once it throws
+		if (!chunks[i].error.empty()) throw std::runtime_error(chunks[i].error);
+		tri_base[i] = ntris;
+		ntris += chunks[i].tris.size();
+	}
+	sc.triangles.resize(ntris);
+	sc.material_ids.resize(ntris);
+	run_threads(nchunks, [&](size_t i) {
+		Chunk& c = chunks[i];
+		for (size_t k = 0; k < c.tris.size(); ++k) {
+			mcpt_triangle tr = c.tris[k];
+			if (with_normals) {
+				mcpt_float4 a = sub4(tr.v[1], tr.v[0]), b = sub4(tr.v[2], tr.v[0]);
+				mcpt_float4 n{0, 0, 0, 0};                       // oclbasic.h:117-125
+				n.x = a.y * b.z - a.z * b.y;
+				n.y = -a.x * b.z + a.z * b.x;
+				n.z = a.x * b.y - a.y * b.x;
+				float s = 0;                                     // 4-lane dot, oclbasic.h:127-135
+				s += n.x * n.x; s += n.y * n.y; s += n.z * n.z; s += n.w * n.w;
+				s = std::sqrt(s);
+				tr.nx = n.x / s; tr.ny = n.y / s; tr.nz = n.z / s;
+				tr.material_id = c.tri_mat[k];
+			}
+			sc.triangles[tri_base[i] + k] = tr;
+			sc.material_ids[tri_base[i] + k] = c.tri_mat[k];
+		}
+	});
+	for (auto& m : mtl) {
+		sc.materials.push_back(classify(m));
+		sc.material_names.push_back(m.name);
 	}
 	return sc;
 }

@@ -27,7 +27,7 @@ EXPORTS = [
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
-    "mcpt_optimize_treelet",
+    "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth",
 ]
 
 
@@ -276,6 +276,16 @@ def build_lbvh(triangles, device=0, return_ms=False):
         raise McptError("mcpt_build_lbvh: %s" % lib().mcpt_last_error().decode())
     assert r == len(nodes)
     return (nodes, ms.value) if return_ms else nodes
+
+
+def measure_read_bandwidth(nbytes, iters=20, device=0):
+    """GB/s of a streaming read over a scratch buffer of nbytes (32 MiB: L2 ceiling; GiBs: HBM ceiling)."""
+    g = ctypes.c_float(0.0)
+    f = lib().mcpt_measure_read_bandwidth
+    f.argtypes = [ctypes.c_int, ctypes.c_size_t, ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
+    if f(int(device), int(nbytes), int(iters), ctypes.byref(g)) < 0:
+        raise McptError("mcpt_measure_read_bandwidth: %s" % lib().mcpt_last_error().decode())
+    return g.value
 
 
 def optimize_treelet(nodes, device=0, return_ms=False):

@@ -51,14 +51,20 @@ class Scene:
     material_ids: np.ndarray   # int32 per triangle
 
 
-def load_object(directory, objname, with_normals=True):
+def load_object(directory, objname, with_normals=True, threads=1):
+    """threads=1: the serial loader (the pinned definition); 0 = all host threads, n = n threads: same bytes."""
     L = lib()
     tr, mt = ctypes.c_void_p(), ctypes.c_void_p()
     ids = ctypes.POINTER(ctypes.c_int)()
     nt, nm = ctypes.c_int(), ctypes.c_int()
-    _check(L.mcpt_host_load_object(directory.encode(), objname.encode(), int(with_normals),
-                                   ctypes.byref(tr), ctypes.byref(nt), ctypes.byref(mt), ctypes.byref(nm),
-                                   ctypes.byref(ids)))
+    if threads == 1:
+        _check(L.mcpt_host_load_object(directory.encode(), objname.encode(), int(with_normals),
+                                       ctypes.byref(tr), ctypes.byref(nt), ctypes.byref(mt), ctypes.byref(nm),
+                                       ctypes.byref(ids)))
+    else:
+        _check(L.mcpt_host_load_object_mt(directory.encode(), objname.encode(), int(with_normals), int(threads),
+                                          ctypes.byref(tr), ctypes.byref(nt), ctypes.byref(mt), ctypes.byref(nm),
+                                          ctypes.byref(ids)))
     try:
         tris = np.frombuffer(ctypes.string_at(tr, nt.value * 64), dtype=T.TRIANGLE).copy()
         mats = np.frombuffer(ctypes.string_at(mt, nm.value * 48), dtype=T.MATERIAL).copy()
