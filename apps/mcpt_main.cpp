@@ -45,6 +45,37 @@ struct State {
 	std::exit(1);
 }
 
+// One model of the BVH quality harness (BVH::TEST::test / testmodel, bvhtest.cpp:448-613): same printed lines,
+// metrics from mcpt_bvh_metrics.  All three "bvhtype" branches of the reference end in the same three numbers.
+void test_model(const mcpt_host_config& cfg, const char* objname, bool with_camera, bool host_bvh) {
+	mcpt_triangle* tris = nullptr;
+	mcpt_material* mats = nullptr;
+	int* ids = nullptr;
+	int ntris = 0, nmats = 0;
+	if (mcpt_host_load_object_mt(cfg.directory, objname, 1, 0, &tris, &ntris, &mats, &nmats, &ids) < 0)
+		die("loadObj", mcpt_host_last_error());
+	std::printf("%s %d\n%s\n", objname, ntris, cfg.bvhtype);
+	std::vector<mcpt_bvh_node> nodes(size_t(2 * ntris - 1));
+	const std::string bvhtype = cfg.bvhtype;
+	if (host_bvh) {
+		if (mcpt_host_build_bvh(tris, ntris, cfg.bvhtype, nodes.data()) < 0) die("BVH", mcpt_host_last_error());
+	} else {
+		if (bvhtype != "hlbvh" && bvhtype != "treelet" && bvhtype != "treeletGPU") die("BVH", "BVH Not Implemented");
+		if (mcpt_build_lbvh(0, tris, ntris, nodes.data(), nullptr) < 0) die("BVH (device)", mcpt_last_error());
+		if (bvhtype != "hlbvh" && mcpt_optimize_treelet(0, nodes.data(), int(nodes.size()), nodes.data(), nullptr) < 0)
+			die("treelet (device)", mcpt_last_error());
+	}
+	mcpt_bvh_quality q{};
+	if (mcpt_bvh_metrics(0, nodes.data(), int(nodes.size()), tris, ntris, with_camera ? &cfg.camera : nullptr,
+	                     cfg.width, cfg.height, &q, nullptr, nullptr) < 0)
+		die("metrics", mcpt_last_error());
+	std::printf("SAH: %g\nEPO_GPU: %g\n", q.sah, q.epo);       // bvhtest.cpp:476,487
+	if (with_camera) std::printf("LCV: %g\n", q.lcv);           // :494
+	mcpt_host_free(tris);
+	mcpt_host_free(mats);
+	mcpt_host_free(ids);
+}
+
 void init(State& s, int ngpus) {
 	if (!s.cfg.opencl) die("config", "Not Implemented");            // raygeneration.cpp:36-38 throws the same
 	if (mcpt_host_load_object_mt(s.cfg.directory, s.cfg.objname, 1, 0, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
@@ -121,7 +152,17 @@ int main(int argc, char** argv) {
 		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch --order-independent-seeds --host-bvh --mis)", a.c_str());
 	}
 	if (mcpt_host_load_config(config.c_str(), configid, &s.cfg) < 0) die("config", mcpt_host_last_error());
-	if (s.cfg.testall || s.cfg.testbvh) die("config", "testbvh/testall (BVH quality harness) is out of scope of this build");
+	if (s.cfg.testall) {                                     // main.cpp:12-15 -> BVH::TEST::testall(), bvhtest.cpp:615-650
+		for (int i = 0; i < s.cfg.nobjs; ++i) {
+			test_model(s.cfg, s.cfg.objs[i], false, s.host_bvh);
+			std::printf("\n");
+		}
+		return 0;
+	}
+	if (s.cfg.testbvh) {                                     // main.cpp:16-19 -> BVH::TEST::test(), bvhtest.cpp:448-530
+		test_model(s.cfg, s.cfg.objname, s.cfg.has_camera != 0, s.host_bvh);
+		return 0;
+	}
 	if (spp_override >= 0) s.cfg.attempt = spp_override;
 	if (gpus < 1) gpus = 1;
 	auto t0 = std::chrono::steady_clock::now();

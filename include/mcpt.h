@@ -164,6 +164,25 @@ int mcpt_build_lbvh(int device, const mcpt_triangle* tris, int ntris, mcpt_bvh_n
  * would not terminate (same condition and message as the host optimiser).  nodes_out may alias nodes_in. */
 int mcpt_optimize_treelet(int device, const mcpt_bvh_node* nodes_in, int nnodes, mcpt_bvh_node* nodes_out, float* build_ms);
 
+/* ---- BVH quality metrics on the device.  Replaces BVH::TEST::SAH / EPO_GPU / LCV of the research
+ * harness (bvhtest.cpp:97-110, :283-321 + kernels/EPO.cl:133-196, :324-444; config "testbvh" / "testall").
+ * sah, epo and lcv hold what the reference functions return (their float results, widened); tris == NULL skips
+ * EPO, camera == NULL skips LCV (the reference skips it without a "camera" entry).  epo_per_leaf / area_per_leaf
+ * (optional, ntris floats, indexed by leaf slot like the kernel's buffers) receive the per-triangle values. */
+typedef struct mcpt_bvh_quality {
+	double sah, epo, lcv;
+	double sah_exact;          /* before narrowing to float */
+	double epo_area;           /* sum of the per-triangle EPO areas */
+	double triangle_area;      /* sum of the triangle areas */
+	double lcv_mean_leaves;    /* mean number of leaf boxes a primary ray touches */
+	uint64_t lcv_rays;
+	float ms_sah, ms_epo, ms_lcv;   /* device time of the three kernels */
+	float pad_;
+} mcpt_bvh_quality;
+int mcpt_bvh_metrics(int device, const mcpt_bvh_node* nodes, int nnodes, const mcpt_triangle* tris, int ntris,
+                     const mcpt_camera* camera, int width, int height, mcpt_bvh_quality* out,
+                     float* epo_per_leaf, float* area_per_leaf);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,6 +37,8 @@ typedef struct mcpt_host_config {
 	int opencl, testbvh, testall, has_camera;
 	int res_x, res_y;     /* camera.resolution */
 	mcpt_camera camera;   /* valid when has_camera */
+	int nobjs;            /* "testall": objname is an array of models under `directory` (config.cpp:91-95) */
+	char objs[32][128];
 } mcpt_host_config;
 
 const char* mcpt_host_last_error(void);

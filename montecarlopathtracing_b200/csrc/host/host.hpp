@@ -45,6 +45,7 @@ struct RenderConfig {
 	std::string bvhtype = "hlbvh";   // "hlbvh" | "treelet" | "treeletGPU" (treated as "treelet")
 	int width = 0, height = 0;
 	std::string directory, objname;
+	std::vector<std::string> objs;   // "testall": objname is an array (config.cpp:91-95)
 	int maxdepth = 0;
 	int attempt = 0;                 // samples per pixel
 	bool opencl = true;              // accepted; false makes the reference throw "Not Implemented"

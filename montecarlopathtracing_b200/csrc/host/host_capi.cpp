@@ -108,6 +108,9 @@ int mcpt_host_load_config(const char* path, int configid, mcpt_host_config* out)
 		out->has_camera = c.has_camera;
 		out->res_x = c.res_x; out->res_y = c.res_y;
 		if (c.has_camera) out->camera = parse_camera(c.camera);
+		if (c.objs.size() > sizeof(out->objs) / sizeof(out->objs[0])) throw std::runtime_error("config: more than 32 models in objname");
+		out->nobjs = int(c.objs.size());
+		for (size_t i = 0; i < c.objs.size(); ++i) put(out->objs[i], sizeof(out->objs[i]), c.objs[i]);
 		return 0;
 	});
 }

@@ -160,7 +160,11 @@ RenderConfig config_from_json(const Json& root, int configid_override) {
 	if (c.has("bvhtype") && !c.at("bvhtype").string().empty()) r.bvhtype = c.at("bvhtype").string();
 	r.testall = c.has("testall") && c.at("testall").boolean();
 	r.directory = c.at("directory").string();
-	if (r.testall) return r;                       // objname is an array in this mode (config.cpp:91-95)
+	if (r.testall) {                               // objname is an array in this mode (config.cpp:91-95)
+		const Json& names = c.at("objname");
+		for (size_t i = 0; i < names.size(); ++i) r.objs.push_back(names.at(i).string());
+		return r;
+	}
 	if (c.has("camera")) { r.camera = c.at("camera"); r.has_camera = r.camera.kind == Json::Object; }
 	r.objname = c.at("objname").string();
 	r.width = int(c.at("width").number());

@@ -27,7 +27,7 @@ EXPORTS = [
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
-    "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth",
+    "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics",
 ]
 
 
@@ -276,6 +276,34 @@ def build_lbvh(triangles, device=0, return_ms=False):
         raise McptError("mcpt_build_lbvh: %s" % lib().mcpt_last_error().decode())
     assert r == len(nodes)
     return (nodes, ms.value) if return_ms else nodes
+
+
+class BvhQuality(ctypes.Structure):
+    _fields_ = [("sah", ctypes.c_double), ("epo", ctypes.c_double), ("lcv", ctypes.c_double),
+                ("sah_exact", ctypes.c_double), ("epo_area", ctypes.c_double), ("triangle_area", ctypes.c_double),
+                ("lcv_mean_leaves", ctypes.c_double), ("lcv_rays", ctypes.c_uint64),
+                ("ms_sah", ctypes.c_float), ("ms_epo", ctypes.c_float), ("ms_lcv", ctypes.c_float), ("pad_", ctypes.c_float)]
+
+
+def bvh_metrics(nodes, triangles=None, camera=None, width=0, height=0, device=0, per_leaf=False):
+    """SAH / EPO / LCV of a node array on the GPU (mcpt_bvh_metrics); dict of the record's fields
+    (+ 'epo_per_leaf', 'area_per_leaf' float32 arrays with per_leaf=True)."""
+    nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE) if triangles is not None else None
+    cam = np.ascontiguousarray(camera) if camera is not None else None
+    q = BvhQuality()
+    epo = np.zeros(len(tr), np.float32) if (per_leaf and tr is not None) else None
+    area = np.zeros(len(tr), np.float32) if (per_leaf and tr is not None) else None
+    r = lib().mcpt_bvh_metrics(int(device), _vp(nd), len(nd), _vp(tr) if tr is not None else None,
+                               len(tr) if tr is not None else 0, _vp(cam) if cam is not None else None,
+                               int(width), int(height), ctypes.byref(q),
+                               _vp(epo) if epo is not None else None, _vp(area) if area is not None else None)
+    if r < 0:
+        raise McptError("mcpt_bvh_metrics: %s" % lib().mcpt_last_error().decode())
+    out = {k: getattr(q, k) for k, _ in BvhQuality._fields_ if k != "pad_"}
+    if per_leaf:
+        out["epo_per_leaf"], out["area_per_leaf"] = epo, area
+    return out
 
 
 def measure_read_bandwidth(nbytes, iters=20, device=0):

@@ -22,7 +22,8 @@ class HostConfigStruct(ctypes.Structure):
                 ("objname", ctypes.c_char * 256), ("width", ctypes.c_int), ("height", ctypes.c_int),
                 ("maxdepth", ctypes.c_int), ("attempt", ctypes.c_int), ("opencl", ctypes.c_int),
                 ("testbvh", ctypes.c_int), ("testall", ctypes.c_int), ("has_camera", ctypes.c_int),
-                ("res_x", ctypes.c_int), ("res_y", ctypes.c_int), ("camera", ctypes.c_uint8 * 80)]
+                ("res_x", ctypes.c_int), ("res_y", ctypes.c_int), ("camera", ctypes.c_uint8 * 80),
+                ("nobjs", ctypes.c_int), ("objs", (ctypes.c_char * 128) * 32)]
 
 
 def lib():
@@ -110,6 +111,7 @@ def load_config(path, configid=-1):
                                     "has_camera", "res_x", "res_y")}
     d.update(bvhtype=s.bvhtype.decode(), directory=s.directory.decode(), objname=s.objname.decode())
     d["camera"] = np.frombuffer(bytes(s.camera), dtype=T.CAMERA).copy()
+    d["objs"] = [s.objs[i].value.decode() for i in range(s.nobjs)]
     return d
 
 

@@ -539,4 +539,110 @@ void oracle_render(const mcpt_camera* cam, int width, int height, const mcpt_bvh
 	if (rays_traced) *rays_traced = traced;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// BVH quality metrics of the research harness: restatement of kernels/EPO.cl:29-196 (per-triangle
+// EPO area, depth-first with the left child popped first) and of the host-side sums of EPO_GPU (bvhtest.cpp:283-321).
+// SAH and LCV have CPU originals in the reference (bvhtest.cpp:97-115, :324-444) which oracle/_ref runs as they are.
+// Deviation: the kernel's point buffers hold 8 vertices, a triangle clipped by six planes can have 9 (the kernel
+// then writes out of bounds); this restatement holds 10 and agrees whenever the kernel is well defined.
+
+struct V3 { float s[3]; };
+
+static int epo_point_in_box(const float* p, const mcpt_float4& lo, const mcpt_float4& hi) {      // EPO.cl:29-40
+	return p[0] >= lo.x && p[0] <= hi.x && p[1] >= lo.y && p[1] <= hi.y && p[2] >= lo.z && p[2] <= hi.z;
+}
+static float epo_half_cross_len(const float* a, const float* b, const float* o) {               // length(cross(a-o, b-o)) * 0.5f
+	const float e1x = a[0] - o[0], e1y = a[1] - o[1], e1z = a[2] - o[2];
+	const float e2x = b[0] - o[0], e2y = b[1] - o[1], e2z = b[2] - o[2];
+	const float cx = e1y * e2z - e1z * e2y, cy = e1z * e2x - e1x * e2z, cz = e1x * e2y - e1y * e2x;
+	return std::sqrt(cx * cx + cy * cy + cz * cz) * 0.5f;
+}
+static void epo_clip(V3* pts, int* size, int axis, float pos, int arg) {                       // roundTr, EPO.cl:43-89
+	if (*size == 0) return;
+	V3 buf[10];
+	int inside[10];
+	const int n = *size;
+	for (int i = 0; i < n; ++i) buf[i] = pts[i];
+	*size = 0;
+	for (int i = 0; i < n; ++i) inside[i] = arg > 0 ? (buf[i].s[axis] >= pos) : (buf[i].s[axis] <= pos);
+	for (int i = 0; i < n; ++i) {
+		const int j = (i + 1 == n) ? 0 : i + 1;
+		if (!inside[i] && !inside[j]) continue;
+		if (inside[i] && inside[j]) { pts[(*size)++] = buf[i]; continue; }
+		if (inside[i]) pts[(*size)++] = buf[i];
+		V3 d{{buf[j].s[0] - buf[i].s[0], buf[j].s[1] - buf[i].s[1], buf[j].s[2] - buf[i].s[2]}};
+		const float t = (pos - buf[i].s[axis]) / d.s[axis];
+		pts[(*size)++] = V3{{buf[i].s[0] + t * d.s[0], buf[i].s[1] + t * d.s[1], buf[i].s[2] + t * d.s[2]}};
+	}
+}
+static float epo_intersect_area(const mcpt_triangle& tr, const mcpt_float4& lo, const mcpt_float4& hi) {   // INTERSECT, EPO.cl:102-130
+	const float* v0 = &tr.v[0].x; const float* v1 = &tr.v[1].x; const float* v2 = &tr.v[2].x;
+	if (epo_point_in_box(v0, lo, hi) && epo_point_in_box(v1, lo, hi) && epo_point_in_box(v2, lo, hi))
+		return epo_half_cross_len(v1, v2, v0);
+	V3 pts[10] = {{{v0[0], v0[1], v0[2]}}, {{v1[0], v1[1], v1[2]}}, {{v2[0], v2[1], v2[2]}}};
+	int n = 3;
+	epo_clip(pts, &n, 0, lo.x, 1); epo_clip(pts, &n, 1, lo.y, 1); epo_clip(pts, &n, 2, lo.z, 1);
+	epo_clip(pts, &n, 0, hi.x, -1); epo_clip(pts, &n, 1, hi.y, -1); epo_clip(pts, &n, 2, hi.z, -1);
+	float ans = 0.0f;                                                                           // pArea, EPO.cl:92-100
+	if (n < 2) return ans;
+	for (int i = 1; i < n - 1; ++i) ans += epo_half_cross_len(pts[i].s, pts[i + 1].s, pts[0].s);
+	return ans;
+}
+
+// calculateEPO, EPO.cl:133-196: one work item per LEAF slot gid (node numPrims-1+gid).  Returns -1 when a path or
+// the to-do stack would exceed the kernel's 128 entries (the kernel only prints a warning and corrupts its stack).
+int oracle_epo_per_leaf(const mcpt_bvh_node* bvh, int nnodes, const mcpt_triangle* tris, int ntris, float* epo, float* area) {
+	const int prims = ntris;
+	if (nnodes != 2 * prims - 1) return -2;
+	int status = 0;
+#pragma omp parallel for schedule(dynamic, 64)
+	for (int gid = 0; gid < prims; ++gid) {
+		const int me = gid + prims - 1;
+		const mcpt_triangle tr = tris[bvh[me].left];
+		int ancestor[128], an = 0, todo[128], ts = 0;
+		bool bad = false;
+		ancestor[an++] = me;
+		for (int p = bvh[me].parent; p != -1; p = bvh[p].parent) {
+			if (an >= 128) { bad = true; break; }
+			ancestor[an++] = p;
+		}
+		float sum = 0.0f;
+		todo[ts++] = 0;
+		while (ts > 0 && !bad) {
+			const int now = todo[--ts];
+			bool skip = false;
+			for (int i = 0; i < an; ++i) if (now == ancestor[i]) { skip = true; break; }
+			bool descend = skip;
+			if (!skip) {
+				const float a = epo_intersect_area(tr, bvh[now].bbmin, bvh[now].bbmax);
+				if (a > 0) {
+					sum += a * (now >= prims - 1 ? 1.0f : 1.2f);
+					descend = true;
+				}
+			}
+			if (descend && bvh[now].left != bvh[now].right) {
+				if (ts + 2 > 128) { bad = true; break; }
+				todo[ts++] = bvh[now].right;
+				todo[ts++] = bvh[now].left;
+			}
+		}
+		if (bad) {
+#pragma omp atomic write
+			status = -1;
+		}
+		epo[gid] = sum;
+		area[gid] = epo_half_cross_len(&tr.v[1].x, &tr.v[2].x, &tr.v[0].x);
+	}
+	return status;
+}
+
+// host half of EPO_GPU (bvhtest.cpp:309-320): sequential double sums, quotient
+double oracle_epo_total(const float* epo, const float* area, int n) {
+	double count = 0.0, a = 0.0;
+	for (int i = 0; i < n; ++i) count += epo[i];
+	for (int i = 0; i < n; ++i) a += area[i];
+	return count / a;
+}
+
 }  // extern "C"

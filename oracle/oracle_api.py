@@ -31,6 +31,7 @@ def oracle():
         L = ctypes.CDLL(build())
         L.oracle_sample_seed.restype = ctypes.c_uint32
         L.oracle_inverse_mismatches.restype = ctypes.c_long
+        L.oracle_epo_total.restype = ctypes.c_double
         _ORACLE = L
     return _ORACLE
 
@@ -45,7 +46,42 @@ def ref():
         if not os.path.exists(so):
             return None
         _REF = ctypes.CDLL(so)
+        for f in ("ref_sah", "ref_epo", "ref_lcv"):
+            if hasattr(_REF, f):
+                getattr(_REF, f).restype = ctypes.c_double
     return _REF
+
+
+# ---------------------------------------------------------------- BVH quality metrics (SURVEY f-4)
+def epo_per_leaf(nodes, tris):
+    """Restatement of kernels/EPO.cl: (epo[ntris], area[ntris]) float32, indexed by leaf slot."""
+    nodes = np.ascontiguousarray(nodes)
+    tris = np.ascontiguousarray(tris)
+    epo = np.zeros(len(tris), np.float32)
+    area = np.zeros(len(tris), np.float32)
+    r = oracle().oracle_epo_per_leaf(_vp(nodes), len(nodes), _vp(tris), len(tris), _vp(epo), _vp(area))
+    if r != 0:
+        raise RuntimeError("oracle_epo_per_leaf: %d" % r)
+    return epo, area
+
+
+def epo_total(epo, area):
+    return oracle().oracle_epo_total(_vp(np.ascontiguousarray(epo, np.float32)), _vp(np.ascontiguousarray(area, np.float32)), len(epo))
+
+
+def ref_sah(nodes):
+    nodes = np.ascontiguousarray(nodes)
+    return ref().ref_sah(_vp(nodes), len(nodes))
+
+
+def ref_epo(nodes, tris):
+    nodes, tris = np.ascontiguousarray(nodes), np.ascontiguousarray(tris)
+    return ref().ref_epo(_vp(nodes), len(nodes), _vp(tris), len(tris))
+
+
+def ref_lcv(nodes, camera, width, height):
+    nodes, camera = np.ascontiguousarray(nodes), np.ascontiguousarray(camera)
+    return ref().ref_lcv(_vp(nodes), len(nodes), _vp(camera), int(width), int(height))
 
 
 # ---------------------------------------------------------------- kernel restatements

@@ -11,6 +11,8 @@
 //   * BVH::TreeletBVH<CPU>               (BVH/treeletBVH.cpp:30-365)
 //   * Auxiliary::parseCamera             (auxiliary.cpp:20-71)
 //   * stbi_write_hdr with vertical flip  (thirdpartywrapper.cpp:14-23)
+//   * BVH::TEST::SAH / EPO / LCV          (bvhtest.cpp:97-115, :120-281, :324-444)  [the CPU metrics; EPO_GPU
+//                                          and test()/testall() compile but need a live OpenCL context]
 // Build recipe: oracle/build_ref.sh (g++ -std=gnu++17 -ffp-contract=off; see that file for the
 // one-line patch of the MSVC-only constructor spelling in hlbvh.cpp).
 #include <algorithm>
@@ -53,10 +55,23 @@ void OpenCLBasic::enqueue1DKernelWithGroupCount(cl::Kernel&, size_t, size_t, con
 	throw "ref_shim: no OpenCL device";
 }
 float OpenCLBasic::timeCost(const cl::Event&, int) { return 0.f; }
+// reached only from bvhtest.cpp's EPO_GPU / test() / testall(), which the shim never calls
+void OpenCLBasic::init() { throw "ref_shim: no OpenCL device"; }
+cl::Context& OpenCLBasic::getContext() { return context; }
+cl::CommandQueue& OpenCLBasic::getQueue() { return queue; }
+void OpenCLBasic::enqueueNDRange(cl::Kernel&, cl::NDRange, cl::NDRange, const std::vector<cl::Event>*, cl::Event*) {
+	throw "ref_shim: no OpenCL device";
+}
+void OpenCLBasic::readBuffer(const cl::Buffer&, void*) { throw "ref_shim: no OpenCL device"; }
 namespace Config {
 static int g_w = 0, g_h = 0;
 int WIDTH() { return g_w; }
 int HEIGHT() { return g_h; }
+nlohmann::json GETCAMERA() { return nlohmann::json(); }
+std::string GETDIRECTORY() { return ""; }
+std::string GETOBJNAME() { return ""; }
+nlohmann::json GETOBJS() { return nlohmann::json::array(); }
+std::string BVHTYPE() { return "hlbvh"; }
 }
 }
 
@@ -65,6 +80,7 @@ int HEIGHT() { return g_h; }
 #include "BVH/treeletBVH.cpp"
 #include "auxiliary.cpp"
 #include "thirdpartywrapper.cpp"
+#include "bvhtest.cpp"
 #include "stb_image_write.h"
 
 using namespace MCPT;
@@ -133,6 +149,31 @@ int ref_parse_camera(const char* json_text, void* out_camera) {
 int ref_write_hdr(const char* path, int w, int h, const float* rgba) {
 	stbi_flip_vertically_on_write(true);
 	return stbi_write_hdr(path, w, h, 4, rgba) ? 0 : -1;
+}
+
+// BVH quality metrics of the research harness, CPU versions (bvhtest.cpp).  LCV casts Config::WIDTH() x HEIGHT()
+// rays, hence the two extra arguments.
+double ref_sah(const void* nodes, int nn) {
+	std::vector<BVHNode> v((const BVHNode*)nodes, (const BVHNode*)nodes + nn);
+	return BVH::TEST::SAH(v);
+}
+double ref_epo(const void* nodes, int nn, const void* tris, int nt) {
+	try {
+		std::vector<BVHNode> v((const BVHNode*)nodes, (const BVHNode*)nodes + nn);
+		std::vector<Triangle> t((const Triangle*)tris, (const Triangle*)tris + nt);
+		std::streambuf* old = std::cout.rdbuf(nullptr);      // the reference prints progress lines
+		float r = BVH::TEST::EPO(v, t);
+		std::cout.rdbuf(old);
+		return r;
+	} catch (...) { return -1.0; }
+}
+double ref_lcv(const void* nodes, int nn, const void* camera, int width, int height) {
+	std::vector<BVHNode> v((const BVHNode*)nodes, (const BVHNode*)nodes + nn);
+	Camera c;
+	memcpy(&c, camera, sizeof(Camera));
+	Config::g_w = width;
+	Config::g_h = height;
+	return BVH::TEST::LCV(v, c);
 }
 
 int ref_sizeof(int which) {

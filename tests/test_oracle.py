@@ -85,3 +85,17 @@ def test_history_skips_zero_samples_and_caps():
     assert cnt.tolist() == [1, 1, 2]                       # zero sample skipped; third pixel already at the cap
     assert new.tolist() == [[5, 5, 5, 0], [2, 4, 6, 0], [3, 3, 3, 0]]
     assert hist[1].tolist() == [2, 4, 6, 0]
+
+
+def test_epo_restatement_close_to_the_reference_cpu_epo():
+    """kernels/EPO.cl restated in the oracle vs BVH::TEST::EPO, the reference's CPU version compiled into oracle/_ref
+    (bvhtest.cpp:120-281).  The CPU version adds every contribution into one float and walks breadth-first, the
+    kernel sums per triangle depth-first: same quantity, equal to about 1e-3."""
+    from oracle import oracle_api as O
+    from montecarlopathtracing_b200 import scenes
+    if O.ref() is None or not hasattr(O.ref(), "ref_epo"):
+        pytest.skip("oracle/_ref not built")
+    sc = scenes.load("veach_mis")
+    epo, area = O.epo_per_leaf(sc.nodes, sc.triangles)
+    assert (area > 0).all() and (epo >= 0).all()
+    assert O.epo_total(epo, area) == pytest.approx(O.ref_epo(sc.nodes, sc.triangles), rel=2e-3)
