@@ -92,24 +92,31 @@ void init(State& s, int ngpus) {
 	if (!s.cfg.has_camera) die("config", "no camera");
 	if (s.cfg.res_x != s.cfg.width || s.cfg.res_y != s.cfg.height)
 		die("config", "camera.resolution must equal width/height (SURVEY A.5)");
+	// one host thread per device: context creation, buffers and uploads overlap; the geometry-derived layout
+	// (SAH tree of the fast walk) is built by the first thread and shared through the library's per-process cache
+	s.ctx.assign(size_t(ngpus), nullptr);
+	std::vector<std::thread> th;
 	for (int g = 0; g < ngpus; ++g) {
-		mcpt_params p{};
-		p.width = s.cfg.width;
-		p.height = s.cfg.height;
-		p.max_depth = s.cfg.maxdepth;
-		p.max_attempt = s.cfg.attempt;
-		p.device = g;
-		p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
-		p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
-		p.run_seed = s.run_seed;
-		p.traversal = MCPT_TRAVERSAL_FAST;
-		mcpt_ctx* c = mcpt_create(&p);
-		if (!c) die("mcpt_create", mcpt_last_error());
-		if (mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size())) ||
-		    mcpt_set_camera(c, &s.cfg.camera))
-			die("scene upload", mcpt_last_error());
-		s.ctx.push_back(c);
+		th.emplace_back([&s, g, ngpus] {
+			mcpt_params p{};
+			p.width = s.cfg.width;
+			p.height = s.cfg.height;
+			p.max_depth = s.cfg.maxdepth;
+			p.max_attempt = s.cfg.attempt;
+			p.device = g;
+			p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
+			p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
+			p.run_seed = s.run_seed;
+			p.traversal = MCPT_TRAVERSAL_FAST;
+			mcpt_ctx* c = mcpt_create(&p);
+			if (!c) die("mcpt_create", mcpt_last_error());
+			if (mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size())) ||
+			    mcpt_set_camera(c, &s.cfg.camera))
+				die("scene upload", mcpt_last_error());
+			s.ctx[size_t(g)] = c;
+		});
 	}
+	for (auto& t : th) t.join();
 }
 
 // Renders `frames` more frames on every device (device g takes its share of the sample indices).

@@ -4,6 +4,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -465,33 +467,26 @@ static int build_emitters(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, con
 	return MCPT_OK;
 }
 
-int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
-                      const mcpt_bvh_node* nodes, int nnodes) {
-	if (int r = check_ctx(c, false, false)) return r;
-	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
-		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
-	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
-	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
-	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
-	    std::memcmp(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
-	    std::memcmp(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
-		for (int m = 0; m < nmats; ++m)
-			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
-				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
-		for (int i = 0; i < ntris; ++i)
-			if (tris[i].material_id < 0 || tris[i].material_id >= nmats)
-				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
-		CU(cudaStreamSynchronize(c->stream));
-		CU(c->mats.alloc(nmats));
-		CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
-		CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
-		CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
-		CU(cudaStreamSynchronize(c->stream));
-		c->scene.materials = c->mats.p;
-		return build_emitters(c, tris, ntris, mats);
-	}
+// Everything mcpt_upload_scene derives from the geometry alone (leaf records, two-box nodes of the reference
+// topology, the binned-SAH tree of the fast walk).  Kept per process for the last scene, so that the N contexts of
+// a multi-GPU run derive it once (the SAH build is the expensive part of an upload).
+struct DerivedScene {
+	std::vector<mcpt_triangle> tris;      // the inputs it was derived from (compared byte for byte)
+	std::vector<mcpt_bvh_node> nodes;
+	int nmats = 0;
+	std::vector<DLeaf> dt;
+	std::vector<DNode> dn, fast;
+	bool contained = true;
+	int fast_depth = 0;
+};
+static std::mutex g_derived_mutex;
+static std::shared_ptr<const DerivedScene> g_derived;
+
+static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats, const mcpt_bvh_node* nodes,
+                 int nnodes, DerivedScene& out) {
 	// ---- validate + derive the traversal layout (host side, once per scene)
-	std::vector<DLeaf> dt(ntris);
+	std::vector<DLeaf>& dt = out.dt;
+	dt.assign(size_t(ntris), DLeaf{});
 	std::memset(dt.data(), 0, dt.size() * sizeof(DLeaf));
 	for (int i = 0; i < ntris; ++i) {
 		const mcpt_triangle& t = tris[i];
@@ -538,9 +533,11 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		}
 		if (rank != ntris) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: the node array does not reach every triangle exactly once");
 	}
-	bool contained = true;
+	bool& contained = out.contained;
+	contained = true;
 	const bool root_leaf = is_leaf(0);
-	std::vector<DNode> dn(root_leaf ? 1 : size_t(nnodes));   // indexed by reference node id (leaf slots unused)
+	std::vector<DNode>& dn = out.dn;                          // indexed by reference node id (leaf slots unused)
+	dn.assign(root_leaf ? 1 : size_t(nnodes), DNode{});
 	std::memset(dn.data(), 0, dn.size() * sizeof(DNode));
 	for (int i = 0; i < nnodes; ++i) {
 		const mcpt_bvh_node& nd = nodes[i];
@@ -564,17 +561,13 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 		d.left = is_leaf(nd.left) ? ~L.left : nd.left;
 		d.right = is_leaf(nd.right) ? ~R.left : nd.right;
 	}
-	// azimuth table of randomDirection (shade.cl:43): angle evaluated in double, narrowed, then cos/sin
-	std::vector<float2> cs(32768);
-	for (int r = 0; r < 32768; ++r) {
-		float deg = float(2 * 3.14159265358979323846 / 32768 * double(uint32_t(r)));
-		cs[r] = make_float2(float(std::cos(double(deg))), float(std::sin(double(deg))));
-	}
-	std::vector<DNode> fast;
+	std::vector<DNode>& fast = out.fast;
+	fast.clear();
 	if (!root_leaf) build_sah_bvh2(dt.data(), ntris, fast);
 	else fast.assign(1, DNode{});
 	// the fast walk pushes at most one entry per level and does not check its stack: verify the depth here
-	int fast_depth = 0;
+	int& fast_depth = out.fast_depth;
+	fast_depth = 0;
 	if (!root_leaf) {
 		std::vector<std::pair<int, int>> todo{{0, 1}};
 		while (!todo.empty()) {
@@ -584,6 +577,66 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 			if (fast[size_t(node)].left >= 0) todo.push_back({fast[size_t(node)].left, d + 1});
 			if (fast[size_t(node)].right >= 0) todo.push_back({fast[size_t(node)].right, d + 1});
 		}
+	}
+	return MCPT_OK;
+}
+
+int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                      const mcpt_bvh_node* nodes, int nnodes) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
+		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
+	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
+	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
+	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
+	    std::memcmp(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
+	    std::memcmp(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
+		for (int m = 0; m < nmats; ++m)
+			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
+				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
+		for (int i = 0; i < ntris; ++i)
+			if (tris[i].material_id < 0 || tris[i].material_id >= nmats)
+				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
+		CU(cudaStreamSynchronize(c->stream));
+		CU(c->mats.alloc(nmats));
+		CU(cudaMemcpyAsync(c->nodes_ref.p, nodes, sizeof(mcpt_bvh_node) * nnodes, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaMemcpyAsync(c->tris_ref.p, tris, sizeof(mcpt_triangle) * ntris, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaMemcpyAsync(c->mats.p, mats, sizeof(mcpt_material) * nmats, cudaMemcpyHostToDevice, c->stream));
+		CU(cudaStreamSynchronize(c->stream));
+		c->scene.materials = c->mats.p;
+		return build_emitters(c, tris, ntris, mats);
+	}
+	// ---- validate + derive the traversal layout (host side, once per scene and process)
+	std::shared_ptr<const DerivedScene> derived;
+	{
+		std::lock_guard<std::mutex> lock(g_derived_mutex);
+		if (g_derived && g_derived->nmats == nmats && g_derived->tris.size() == size_t(ntris) && g_derived->nodes.size() == size_t(nnodes) &&
+		    std::memcmp(g_derived->tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
+		    std::memcmp(g_derived->nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
+			derived = g_derived;
+		} else {
+			auto fresh = std::make_shared<DerivedScene>();
+			if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, *fresh)) return r;
+			fresh->tris.assign(tris, tris + ntris);
+			fresh->nodes.assign(nodes, nodes + nnodes);
+			fresh->nmats = nmats;
+			derived = g_derived = fresh;
+		}
+	}
+	for (int m = 0; m < nmats; ++m)
+		if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
+			return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
+	const std::vector<DLeaf>& dt = derived->dt;
+	const std::vector<DNode>& dn = derived->dn;
+	std::vector<DNode> fast = derived->fast;        // copied: the leaf links are re-encoded below
+	const bool contained = derived->contained;
+	const bool root_leaf = nodes[0].left == nodes[0].right;
+	const int fast_depth = derived->fast_depth;
+	// azimuth table of randomDirection (shade.cl:43): angle evaluated in double, narrowed, then cos/sin
+	std::vector<float2> cs(32768);
+	for (int r = 0; r < 32768; ++r) {
+		float deg = float(2 * 3.14159265358979323846 / 32768 * double(uint32_t(r)));
+		cs[r] = make_float2(float(std::cos(double(deg))), float(std::sin(double(deg))));
 	}
 	const bool fast_too_deep = fast_depth > STACK_SIZE;
 	// the experimental 8-wide layout is derived on first use (ensure_wide), not on every upload
