@@ -75,25 +75,38 @@ def ensure_built():
 
 
 def cpu_sample(a, min_seconds=10.0, max_passes=8):
-    """Oracle (port of the reference kernels) on all host cores: 1-spp passes of a 960x540 view of the
-    same scene/camera/depth until min_seconds of work are done."""
+    """The reference's CPU implementation of the path on all host cores: 1-spp passes of a 960x540 view of the same
+    scene/camera/depth until min_seconds of work are done.  kind "reference": the reference's OWN kernel sources
+    compiled as C++ (oracle/_ref/libmcpt_refcl.so, built by oracle/build_ref.sh where /root/reference exists and
+    shipped prebuilt to the GPU box) driven like OpenCL::update; kind "port": the oracle's restatement, used only
+    where that library was never built."""
     from montecarlopathtracing_b200 import scenes
     from oracle import oracle_api as O
     sc = scenes.load(a.scene)
     cores = O.set_threads()              # all host cores, even under torchrun's OMP_NUM_THREADS=1
     w, h = max(1, a.width // 2), max(1, a.height // 2)
+    use_ref = O.refcl() is not None
+    if use_ref:
+        O.refcl().refcl_set_threads(cores)
+        seeds = O.init_seeds(w * h, 1)
+        hist = np.zeros((w * h, 4), np.float32)
+        counts = np.zeros(w * h, np.int32)
     rays = paths = 0
     t0 = time.perf_counter()
     passes = 0
     while passes < max_passes and (passes == 0 or time.perf_counter() - t0 < min_seconds):
-        r = O.render(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, a.depth, 1 << 20, 1, seed_mode=1,
-                     run_seed=1, first_sample=passes)
-        rays += r["rays_traced"]
+        if use_ref:
+            rays += O.refcl_update(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, a.depth, 1 << 20, 1, seeds, hist, counts)
+        else:
+            r = O.render(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, a.depth, 1 << 20, 1, seed_mode=1,
+                         run_seed=1, first_sample=passes)
+            rays += r["rays_traced"]
         paths += w * h
         passes += 1
     dt = time.perf_counter() - t0
-    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
-            "sample": "%dx%d, %d spp, depth %d, same scene and camera (%.1f s of CPU work)" % (w, h, passes, a.depth, dt),
+    return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference" if use_ref else "port",
+            "sample": "%dx%d, %d spp, depth %d, same scene and camera (%.1f s of CPU work)%s" %
+                      (w, h, passes, a.depth, dt, ", the reference's kernels/*.cl compiled as C++ with OpenMP over work items" if use_ref else ""),
             "mpaths_per_s": paths / dt / 1e6}, rays, paths, dt
 
 
@@ -112,7 +125,8 @@ def run_reference(a):
         tot_paths += paths
         tot_dt += dt
     v = tot_rays / tot_dt / 1e6
-    last.update(value=v, sample="%dx%d, 1 spp per step, depth %d, same scene and camera" % (a.width // 2, a.height // 2, a.depth),
+    last.update(value=v, sample="%dx%d, 1 spp per step, depth %d, same scene and camera%s" %
+                (a.width // 2, a.height // 2, a.depth, ", the reference's kernels/*.cl compiled as C++ with OpenMP over work items" if last["kind"] == "reference" else ""),
                 mpaths_per_s=tot_paths / tot_dt / 1e6)
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": a.gpus,
                       "steps": a.steps, "warmup": a.warmup, "ms_per_step": tot_dt / a.steps * 1e3,

@@ -30,3 +30,20 @@ g++ $CXXFLAGS -c "$REF/tiny_obj_loader.cpp" -o "$OUT/tiny_obj_loader.o"
 g++ $CXXFLAGS -c "$REF/stb_image_write.cpp" -o "$OUT/stb_image_write.o"
 g++ -shared -o "$OUT/libmcpt_ref.so" "$OUT/ref_shim.o" "$OUT/tiny_obj_loader.o" "$OUT/stb_image_write.o" $OCL
 echo "build_ref: wrote $OUT/libmcpt_ref.so"
+
+# ---- the reference's OpenCL kernels compiled as C++ (oracle/ref_kernels.cpp + oracle/clc_shim.hpp).
+# Adapted copies go to oracle/_ref/src/ (never into the repository).  The adaptations are purely syntactic:
+#   1. `(floatN)(a, b, ...)` / `(int2)(a, b)` vector literals -> make_floatN(a, b, ...) / make_int2(a, b): C++ reads the
+#      OpenCL form as a cast of a comma expression;
+#   2. objdef.h: `#ifdef __cplusplus` -> `#if 0`, `#ifndef __cplusplus` -> `#if 1`, i.e. the branch an OpenCL compiler
+#      sees (record definitions without the host namespace, EPSILON = 1e-5f, the device functions);
+#   3. `a.s012 = b.s012;` -> `a.s012 = make_float3(b.s012);` (shade.cl:185): the swizzle view keeps its trivial copy
+#      assignment so that the records stay trivially copyable; routing the right side through float3 selects the
+#      three-lane assignment OpenCL performs.
+CLSED='s/(float\(2\|3\|4\|16\))(/make_float\1(/g; s/(int2)(/make_int2(/g; s/\.s012 = \(.*\)\.s012;/.s012 = make_float3(\1.s012);/'
+sed "$CLSED; s/#ifdef __cplusplus/#if 0/; s/#ifndef __cplusplus/#if 1/" "$REF/objdef.h" > "$OUT/src/objdef_cl.h"
+for k in rayGenerator intersect shade history testkernel; do
+  sed "$CLSED" "$REF/kernels/$k.cl" > "$OUT/src/${k}_cl.inc"
+done
+g++ -std=gnu++17 -O2 -fPIC -fopenmp -ffp-contract=off -w -I"$HERE" -I"$OUT/src" -shared -o "$OUT/libmcpt_refcl.so" "$HERE/ref_kernels.cpp"
+echo "build_ref: wrote $OUT/libmcpt_refcl.so"

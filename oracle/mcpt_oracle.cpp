@@ -11,11 +11,16 @@
 //   K5 display            kernels/testkernel.cl:9-14
 //   frame loop            OpenCLApp.cpp:57-82, colorout.cpp:40-73
 //
-// PARITY PINNING: the reference has no tests, golden vectors or fixtures for this path
-//  and its kernels cannot run in this container, so the kernel restatement is
-// "parity unpinned" by reference outputs.  What IS pinned by the reference's own code (compiled
-// into oracle/_ref): struct layouts, scene loading, material classification, camera basis, the
-// LBVH node array and the .hdr bytes.  tests/golden/ holds outputs of THIS oracle.
+// PARITY PINNING: the reference has no tests, golden vectors or fixtures for this path and no
+// OpenCL platform exists here, so the pin is the reference's OWN kernel source: oracle/build_ref.sh compiles
+// kernels/*.cl and the device half of objdef.h as C++ (oracle/ref_kernels.cpp, oracle/clc_shim.hpp; three syntactic
+// adaptations, listed in build_ref.sh) into oracle/_ref/libmcpt_refcl.so, and tests/test_reference_kernels.py holds
+// every buffer this restatement produces - rays, hits incl. the raw triangleID field, colour, seeds, history,
+// counts, display - bit-equal to it on the three scenes, all four material types, random and adversarial rays.
+// What that pin cannot cover is OpenCL's implementation-defined part (next paragraph): both sides use the same
+// stated conventions for the built-ins.  The host side is pinned by the reference's own host code (oracle/_ref/
+// libmcpt_ref.so): struct layouts, scene loading, material classification, camera basis, LBVH and treelet node
+// arrays, .hdr bytes, SAH / EPO / LCV.  tests/golden/ holds outputs of this oracle and of those libraries.
 //
 // Implementation-defined OpenCL behaviour is fixed here once (and mirrored by the CUDA kernels):
 //   * no FMA contraction (build with -ffp-contract=off); + - * / sqrt are IEEE round-to-nearest

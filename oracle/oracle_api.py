@@ -52,6 +52,64 @@ def ref():
     return _REF
 
 
+_REFCL = None
+
+
+def refcl():
+    """The reference's own OpenCL kernel sources compiled as C++ (oracle/ref_kernels.cpp); None where oracle/_ref
+    was never built (no /root/reference and no prebuilt library)."""
+    global _REFCL
+    if _REFCL is None:
+        so = os.path.join(_HERE, "_ref", "libmcpt_refcl.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["bash", os.path.join(_HERE, "build_ref.sh")])
+        if not os.path.exists(so):
+            return None
+        _REFCL = ctypes.CDLL(so)
+    return _REFCL
+
+
+def refcl_generate_rays(camera, width, height):
+    from montecarlopathtracing_b200 import types as T
+    rays = np.zeros(width * height, dtype=T.RAY)
+    cam = np.ascontiguousarray(camera).copy()
+    refcl().refcl_generate_rays(_vp(cam), width, height, _vp(rays))
+    return rays
+
+
+def refcl_intersect(rays, nodes, tris, tmin=0.001, hits=None):
+    from montecarlopathtracing_b200 import types as T
+    if hits is None:
+        hits = np.zeros(len(rays), dtype=T.HIT)
+    refcl().refcl_intersect(_vp(rays), _vp(nodes), _vp(tris), _vp(hits), ctypes.c_long(len(rays)), ctypes.c_float(tmin))
+    return hits
+
+
+def refcl_shade(materials, rays, hits, color, seeds, max_depth):
+    refcl().refcl_shade(_vp(materials), _vp(rays), _vp(hits), _vp(color), _vp(seeds), ctypes.c_long(len(rays)), max_depth)
+
+
+def refcl_history(new_colors, histories, counts, width, height, max_attempt):
+    refcl().refcl_history(_vp(new_colors), _vp(histories), _vp(counts), width, height, max_attempt)
+
+
+def refcl_update(camera, width, height, nodes, tris, materials, max_depth, max_attempt, frames, seeds, hist, counts,
+                 tmin=0.001):
+    """`frames` iterations of OpenCL::update with the reference's kernels; seeds / hist / counts are updated in place.
+    Returns the number of live rays that entered intersect."""
+    traced = ctypes.c_ulonglong(0)
+    cam = np.ascontiguousarray(camera).copy()
+    refcl().refcl_update(_vp(cam), width, height, _vp(nodes), _vp(tris), _vp(materials), max_depth, max_attempt, frames,
+                         ctypes.c_float(tmin), _vp(seeds), _vp(hist), _vp(counts), ctypes.byref(traced))
+    return traced.value
+
+
+def refcl_display(color, width, height):
+    out = np.zeros_like(color)
+    refcl().refcl_display(_vp(color), _vp(out), width, height)
+    return out
+
+
 # ---------------------------------------------------------------- BVH quality metrics (SURVEY f-4)
 def epo_per_leaf(nodes, tris):
     """Restatement of kernels/EPO.cl: (epo[ntris], area[ntris]) float32, indexed by leaf slot."""

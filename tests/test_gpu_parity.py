@@ -153,6 +153,51 @@ def test_stage_loop_bit_exact(name, request):
         assert np.max(np.abs(disp - ref_disp)) <= 1e-6
 
 
+@pytest.mark.skipif(O.refcl() is None, reason="oracle/_ref/libmcpt_refcl.so not built")
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_stage_loop_equals_the_reference_kernels(name, request):
+    """The same loop against the reference's OWN kernels/*.cl (compiled as C++ into oracle/_ref/libmcpt_refcl.so):
+    CUDA stage kernels -> reference kernel source, without the restatement in between."""
+    sc = request.getfixturevalue(name)
+    w, h = (96, 96) if name == "cbox" else (128, 72)
+    n = w * h
+    depth = 8
+    with _ctx(sc, w, h, max_depth=depth, max_attempt=2, run_seed=9) as ctx:
+        seeds = O.init_seeds(n, 9)
+        hist = np.zeros((n, 4), np.float32)
+        counts = np.zeros(n, np.int32)
+        for frame in range(3):
+            rays = O.refcl_generate_rays(sc.camera, w, h)
+            color = np.ones((n, 4), np.float32)
+            hits = np.zeros(n, T.HIT)
+            ctx.reset_color()
+            ctx.generate_rays()
+            assert ctx.read_rays().tobytes() == rays.tobytes()
+            for d in range(depth):
+                live = (rays["state"].view(np.uint32) & 0xFF000000) == 0
+                O.refcl_intersect(rays, sc.nodes, sc.triangles, hits=hits)
+                ctx.intersect(device.TRAVERSAL_FAST)
+                g_hits = ctx.read_hits()
+                for f in ("normal", "point", "t", "material_id"):
+                    assert g_hits[f][live].tobytes() == hits[f][live].tobytes(), (frame, d, f)
+                O.refcl_shade(sc.materials, rays, hits, color, seeds, depth)
+                ctx.shade()
+                g_rays = ctx.read_rays()
+                for f in ("origin", "state", "direction", "pixel"):
+                    assert g_rays[f].tobytes() == rays[f].tobytes(), (frame, d, f)
+                assert ctx.read_color().tobytes() == color.tobytes(), (frame, d)
+                assert np.array_equal(ctx.read_seeds(), seeds), (frame, d)
+            O.refcl_history(color, hist, counts, w, h, 2)
+            ctx.accumulate()
+            g_hist, g_counts = ctx.read_history()
+            assert g_hist.tobytes() == hist.tobytes() and np.array_equal(g_counts, counts)
+        # the product path (fused wavefront render) against the reference kernels' loop
+    with _ctx(sc, w, h, max_depth=depth, max_attempt=2, run_seed=9) as ctx:
+        ctx.render(3)
+        g_hist, g_counts = ctx.read_history()
+        assert g_hist.tobytes() == hist.tobytes() and np.array_equal(g_counts, counts)
+
+
 @pytest.mark.parametrize("name,seed_mode,sif", [("cbox", 0, 0), ("cbox", 1, 4), ("mis", 0, 0), ("mis", 1, 3)])
 def test_render_bit_exact(name, seed_mode, sif, request):
     """Fused wavefront render == oracle render of the same seeds (running mean, counts, ray count)."""
