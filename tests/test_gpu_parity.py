@@ -177,7 +177,7 @@ def test_stage_loop_equals_the_reference_kernels(name, request):
                 live = (rays["state"].view(np.uint32) & 0xFF000000) == 0
                 O.refcl_intersect(rays, sc.nodes, sc.triangles, hits=hits)
                 ctx.intersect(device.TRAVERSAL_FAST)
-                g_hits = ctx.read_hits()
+                g_hits, _ = ctx.read_hits()
                 for f in ("normal", "point", "t", "material_id"):
                     assert g_hits[f][live].tobytes() == hits[f][live].tobytes(), (frame, d, f)
                 O.refcl_shade(sc.materials, rays, hits, color, seeds, depth)
