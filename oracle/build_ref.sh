@@ -42,7 +42,7 @@ echo "build_ref: wrote $OUT/libmcpt_ref.so"
 #      three-lane assignment OpenCL performs.
 CLSED='s/(float\(2\|3\|4\|16\))(/make_float\1(/g; s/(int2)(/make_int2(/g; s/\.s012 = \(.*\)\.s012;/.s012 = make_float3(\1.s012);/'
 sed "$CLSED; s/#ifdef __cplusplus/#if 0/; s/#ifndef __cplusplus/#if 1/" "$REF/objdef.h" > "$OUT/src/objdef_cl.h"
-for k in rayGenerator intersect shade history testkernel; do
+for k in rayGenerator intersect shade history testkernel EPO; do
   sed "$CLSED" "$REF/kernels/$k.cl" > "$OUT/src/${k}_cl.inc"
 done
 g++ -std=gnu++17 -O2 -fPIC -fopenmp -ffp-contract=off -w -I"$HERE" -I"$OUT/src" -shared -o "$OUT/libmcpt_refcl.so" "$HERE/ref_kernels.cpp"

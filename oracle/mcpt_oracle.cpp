@@ -563,6 +563,15 @@ static float epo_half_cross_len(const float* a, const float* b, const float* o) 
 	const float cx = e1y * e2z - e1z * e2y, cy = e1z * e2x - e1x * e2z, cz = e1x * e2y - e1y * e2x;
 	return std::sqrt(cx * cx + cy * cy + cz * cz) * 0.5f;
 }
+static int g_epo_max_polygon = 0;       // largest vertex count any clip pass produced (the kernel's buffers hold 8)
+static void epo_clip(V3* pts, int* size, int axis, float pos, int arg);
+static void epo_clip_tracked(V3* pts, int* size, int axis, float pos, int arg) {
+	epo_clip(pts, size, axis, pos, arg);
+	if (*size > g_epo_max_polygon) {
+#pragma omp critical
+		if (*size > g_epo_max_polygon) g_epo_max_polygon = *size;
+	}
+}
 static void epo_clip(V3* pts, int* size, int axis, float pos, int arg) {                       // roundTr, EPO.cl:43-89
 	if (*size == 0) return;
 	V3 buf[10];
@@ -587,8 +596,8 @@ static float epo_intersect_area(const mcpt_triangle& tr, const mcpt_float4& lo, 
 		return epo_half_cross_len(v1, v2, v0);
 	V3 pts[10] = {{{v0[0], v0[1], v0[2]}}, {{v1[0], v1[1], v1[2]}}, {{v2[0], v2[1], v2[2]}}};
 	int n = 3;
-	epo_clip(pts, &n, 0, lo.x, 1); epo_clip(pts, &n, 1, lo.y, 1); epo_clip(pts, &n, 2, lo.z, 1);
-	epo_clip(pts, &n, 0, hi.x, -1); epo_clip(pts, &n, 1, hi.y, -1); epo_clip(pts, &n, 2, hi.z, -1);
+	epo_clip_tracked(pts, &n, 0, lo.x, 1); epo_clip_tracked(pts, &n, 1, lo.y, 1); epo_clip_tracked(pts, &n, 2, lo.z, 1);
+	epo_clip_tracked(pts, &n, 0, hi.x, -1); epo_clip_tracked(pts, &n, 1, hi.y, -1); epo_clip_tracked(pts, &n, 2, hi.z, -1);
 	float ans = 0.0f;                                                                           // pArea, EPO.cl:92-100
 	if (n < 2) return ans;
 	for (int i = 1; i < n - 1; ++i) ans += epo_half_cross_len(pts[i].s, pts[i + 1].s, pts[0].s);
@@ -640,6 +649,13 @@ int oracle_epo_per_leaf(const mcpt_bvh_node* bvh, int nnodes, const mcpt_triangl
 		area[gid] = epo_half_cross_len(&tr.v[1].x, &tr.v[2].x, &tr.v[0].x);
 	}
 	return status;
+}
+
+// largest clipped polygon since the last reset: above 8 the reference kernel itself is undefined (buffer overflow)
+int oracle_epo_max_polygon(int reset) {
+	const int m = g_epo_max_polygon;
+	if (reset) g_epo_max_polygon = 0;
+	return m;
 }
 
 // host half of EPO_GPU (bvhtest.cpp:309-320): sequential double sums, quotient

@@ -123,6 +123,20 @@ def epo_per_leaf(nodes, tris):
     return epo, area
 
 
+def epo_max_polygon(reset=True):
+    """Largest clipped polygon the restatement has seen since the last reset (the reference kernel's buffers hold 8)."""
+    return oracle().oracle_epo_max_polygon(int(reset))
+
+
+def refcl_epo(nodes, tris):
+    """kernels/EPO.cl itself (compiled as C++): (epo[ntris], area[ntris])."""
+    nodes, tris = np.ascontiguousarray(nodes).copy(), np.ascontiguousarray(tris).copy()
+    epo = np.zeros(len(tris), np.float32)
+    area = np.zeros(len(tris), np.float32)
+    refcl().refcl_epo(_vp(nodes), _vp(tris), _vp(epo), _vp(area), len(tris))
+    return epo, area
+
+
 def epo_total(epo, area):
     return oracle().oracle_epo_total(_vp(np.ascontiguousarray(epo, np.float32)), _vp(np.ascontiguousarray(area, np.float32)), len(epo))
 

@@ -3,6 +3,7 @@
 // through it, the CUDA kernels against the reference's code:
 //   kernels/rayGenerator.cl  generateRay      kernels/intersect.cl  intersectRays (+ objdef.h:101-276)
 //   kernels/shade.cl         shade            kernels/history.cl    func          kernels/testkernel.cl  func
+//   kernels/EPO.cl           calculateEPO (BVH quality harness, SURVEY f-4)
 // The sources are read where they lie under /root/reference; oracle/build_ref.sh writes syntactically adapted copies
 // to oracle/_ref/src/ (git-ignored) - the adaptations are listed there - and oracle/clc_shim.hpp supplies the OpenCL C
 // vocabulary, including the conventions chosen for OpenCL's implementation-defined built-ins.
@@ -38,6 +39,9 @@ namespace hist {
 }
 namespace disp {
 #include "testkernel_cl.inc"
+}
+namespace epo {
+#include "EPO_cl.inc"
 }
 
 static_assert(sizeof(Camera) == 80 && sizeof(Ray) == 48 && sizeof(Hit) == 48 && sizeof(Triangle) == 64 &&
@@ -135,6 +139,16 @@ void refcl_update(void* camera, int width, int height, void* nodes, void* tris, 
 	delete[] rays;
 	delete[] hits;
 	delete[] color;
+}
+
+// EPO_GPU's kernel launch (bvhtest.cpp:296-300): NDRange (triCount).  The kernel's point buffers hold 8 vertices;
+// callers must not pass scenes where a clipped polygon reaches 9 (oracle_epo_max_polygon tells).
+void refcl_epo(void* nodes, void* tris, void* epo, void* area, int ntris) {
+#pragma omp parallel for schedule(dynamic, 64)
+	for (int i = 0; i < ntris; ++i) {
+		item1(size_t(i), size_t(ntris));
+		epo::calculateEPO(static_cast<BVHNode*>(nodes), static_cast<Triangle*>(tris), static_cast<float*>(epo), static_cast<float*>(area), uint(ntris));
+	}
 }
 
 void refcl_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }

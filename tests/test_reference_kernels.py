@@ -100,3 +100,18 @@ def test_render_entry_point_equals_the_kernel_loop():
     traced = O.refcl_update(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, depth, attempt, frames, seeds2, hist2, cnt2)
     assert hist2.tobytes() == hist.tobytes() and np.array_equal(cnt2, cnt) and np.array_equal(seeds2, seeds)
     assert traced == out["rays_traced"]
+
+
+@pytest.mark.parametrize("name", ["cbox", "veach_mis"])
+def test_epo_kernel(name):
+    """kernels/EPO.cl (BVH quality harness, SURVEY f-4): per-leaf EPO and triangle areas of the restatement equal the
+    kernel's, on the LBVH and on the treelet-optimised tree; then the host sums of EPO_GPU (bvhtest.cpp:309-320)."""
+    from montecarlopathtracing_b200 import host
+    sc = scenes.load(name)
+    for nodes in (sc.nodes, host.treelet(sc.nodes)):
+        O.epo_max_polygon()
+        epo, area = O.epo_per_leaf(nodes, sc.triangles)
+        assert O.epo_max_polygon() <= 8            # above 8 the kernel's own point buffers overflow
+        k_epo, k_area = O.refcl_epo(nodes, sc.triangles)
+        assert epo.tobytes() == k_epo.tobytes() and area.tobytes() == k_area.tobytes()
+        assert O.epo_total(epo, area) > 0
