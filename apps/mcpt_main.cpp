@@ -190,10 +190,11 @@ int main(int argc, char** argv) {
 		if (mcpt_read_history(s.ctx[0], img.data(), nullptr)) die("readback", mcpt_last_error());
 		mcpt_get_stats(s.ctx[0], &tot);
 	} else {
-		std::vector<double> acc(7 * npix, 0.0), part(7 * npix);
+		// one merge on GPU 0 over NVLink peer memory, one readback (the sums never pass through host memory per GPU)
+		std::vector<double> acc(7 * npix, 0.0);
+		if (s.ctx.size() > 1 && mcpt_merge_sums(s.ctx[0], s.ctx.data() + 1, int(s.ctx.size()) - 1)) die("merge", mcpt_last_error());
+		if (mcpt_read_sums(s.ctx[0], acc.data())) die("readback", mcpt_last_error());
 		for (mcpt_ctx* c : s.ctx) {
-			if (mcpt_read_sums(c, part.data())) die("readback", mcpt_last_error());
-			for (size_t k = 0; k < acc.size(); ++k) acc[k] += part[k];
 			mcpt_stats st{};
 			mcpt_get_stats(c, &st);
 			tot.rays_traced += st.rays_traced;
@@ -204,6 +205,7 @@ int main(int argc, char** argv) {
 			for (int k = 0; k < 3; ++k) img[4 * p + k] = float(acc[k * npix + p] / n);
 		}
 	}
+	auto t3 = std::chrono::steady_clock::now();
 	std::string base = out_prefix.empty() ? std::string(s.cfg.objname) : out_prefix;
 	if (mcpt_host_write_hdr((base + ".hdr").c_str(), s.cfg.width, s.cfg.height, img.data()) < 0 ||
 	    mcpt_host_write_png((base + ".png").c_str(), s.cfg.width, s.cfg.height, img.data()) < 0)
@@ -211,9 +213,9 @@ int main(int argc, char** argv) {
 	double sec = std::chrono::duration<double>(t2 - t1).count();
 	std::printf("Finished Attempting\n");                                    // colorout.cpp:65
 	std::printf("{\"scene\": \"%s%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"gpus\": %d, \"init_s\": %.3f, "
-	            "\"render_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
+	            "\"render_s\": %.3f, \"merge_read_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
 	            s.cfg.directory, s.cfg.objname, s.cfg.width, s.cfg.height, frames, gpus,
-	            std::chrono::duration<double>(t1 - t0).count(), sec, tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
+	            std::chrono::duration<double>(t1 - t0).count(), sec, std::chrono::duration<double>(t3 - t2).count(), tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
 	for (mcpt_ctx* c : s.ctx) mcpt_destroy(c);
 	mcpt_host_free(s.tris);
 	mcpt_host_free(s.mats);

@@ -129,6 +129,12 @@ int mcpt_read_sums(mcpt_ctx* ctx, double* dst);
 /* Accumulate the sums in caller-owned DEVICE memory (7*W*H doubles, e.g. the NCCL reduce buffer); NULL = own. */
 int mcpt_bind_sums(mcpt_ctx* ctx, double* device_ptr);
 
+/* Multi-GPU merge of the sample sums: dst.sums += srcs[0].sums + srcs[1].sums + ... in this order, by one
+ * kernel on dst's device that reads the other contexts' accumulators in place over NVLink peer mappings (staged with
+ * cudaMemcpyPeer where a peer cannot be mapped).  Stands where the reference would need one reduce per output frame;
+ * synchronises every context involved.  Follow with mcpt_read_sums(dst). */
+int mcpt_merge_sums(mcpt_ctx* dst, mcpt_ctx* const* srcs, int nsrc);
+
 /* ---- intersection microbench / ad-hoc queries against the uploaded scene ---- */
 /* host buffers: copies in, traces n rays, copies out (hits 48 B each; closest may be NULL) */
 int mcpt_trace(mcpt_ctx* ctx, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_t* closest, int traversal);

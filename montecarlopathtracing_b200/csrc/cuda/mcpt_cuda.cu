@@ -901,6 +901,47 @@ int mcpt_bind_sums(mcpt_ctx* c, double* device_ptr) {
 	return MCPT_OK;
 }
 
+// ---------------------------------------------------------------- multi-GPU merge over peer memory
+// dst.sums += src_0.sums + src_1.sums + ... (in this order, so the doubles equal a host-side merge in context order).
+// One kernel on dst's device reads the peers' accumulators in place through NVLink peer mappings; peers that cannot
+// be mapped are staged through a device buffer with cudaMemcpyPeer.  No host copy of the 56 B/pixel sums.
+int mcpt_merge_sums(mcpt_ctx* dst, mcpt_ctx* const* srcs, int nsrc) {
+	if (int r = check_ctx(dst, false, false)) return r;
+	if (nsrc < 0 || nsrc > MERGE_MAX_PEERS || (nsrc > 0 && !srcs))
+		return fail(MCPT_ERR_ARG, "mcpt_merge_sums: expected 0..15 source contexts");
+	const size_t count = 7 * size_t(dst->npix);
+	MergePeers peers{};
+	std::vector<DevBuf<double>> staged(static_cast<size_t>(nsrc));
+	for (int k = 0; k < nsrc; ++k) {
+		mcpt_ctx* s = srcs[k];
+		if (!s || s == dst || s->npix != dst->npix) return fail(MCPT_ERR_ARG, "mcpt_merge_sums: sources must be other contexts of the same resolution");
+		CU(cudaSetDevice(s->prm.device));
+		CU(cudaStreamSynchronize(s->stream));              // the peer's samples are complete
+		CU(cudaSetDevice(dst->prm.device));
+		const double* ptr = s->sums;
+		if (s->prm.device != dst->prm.device) {
+			int can = 0;
+			CU(cudaDeviceCanAccessPeer(&can, dst->prm.device, s->prm.device));
+			cudaError_t e = can ? cudaDeviceEnablePeerAccess(s->prm.device, 0) : cudaErrorPeerAccessUnsupported;
+			if (e == cudaErrorPeerAccessAlreadyEnabled) { e = cudaSuccess; (void)cudaGetLastError(); }
+			if (e != cudaSuccess) {                         // no peer mapping: stage the plane set on dst's device
+				(void)cudaGetLastError();
+				CU(staged[size_t(k)].alloc(count));
+				CU(cudaMemcpyPeerAsync(staged[size_t(k)].p, dst->prm.device, s->sums, s->prm.device, sizeof(double) * count, dst->stream));
+				ptr = staged[size_t(k)].p;
+			}
+		}
+		peers.p[k] = ptr;
+	}
+	peers.n = nsrc;
+	if (nsrc > 0) {
+		k_merge_sums<<<dst->persistent_grid(256), 256, 0, dst->stream>>>(dst->sums, peers, count);
+		CU(cudaGetLastError());
+	}
+	CU(cudaStreamSynchronize(dst->stream));
+	return MCPT_OK;
+}
+
 // ---------------------------------------------------------------- microbench / ad-hoc queries
 int mcpt_trace_device(mcpt_ctx* c, const mcpt_ray* d_rays, long n, mcpt_hit* d_hits, int32_t* d_closest, int traversal) {
 	if (int r = check_ctx(c, true, false)) return r;

@@ -551,4 +551,18 @@ __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_bounce_persistent
 	persistent_walk(sc, tmin, total, head, job);
 }
 
+// ---- multi-GPU merge: acc[i] += peer_0[i] + peer_1[i] + ... with the peers' accumulators read in place over
+// NVLink peer mappings (mcpt_merge_sums).  Streaming, 8 B per element and peer; peers are added in index order.
+constexpr int MERGE_MAX_PEERS = 15;
+struct MergePeers { const double* p[MERGE_MAX_PEERS]; int n; };
+__global__ void __launch_bounds__(256) k_merge_sums(double* __restrict__ acc, MergePeers peers, size_t count) {
+	const size_t stride = size_t(gridDim.x) * blockDim.x;
+	for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < count; i += stride) {
+		double v = acc[i];
+#pragma unroll 1
+		for (int k = 0; k < peers.n; ++k) v += __ldcs(peers.p[k] + i);
+		acc[i] = v;
+	}
+}
+
 }  // namespace mcpt

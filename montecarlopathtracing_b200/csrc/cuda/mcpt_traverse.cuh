@@ -463,8 +463,29 @@ __device__ __forceinline__ void walk2_init(Walk2& w, const SceneDev& sc, const R
 
 __device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur == WALK_DONE && w.pending == 0; }
 
+// The walk's stack lives in local memory: every push / pop is an LSU access whose lines also compete for L1 and,
+// written through, for L2 (ncu r1n: 26% of the kernel's L1 wavefronts, 16% of its L2 requests).  MCPT_SHARED_STACK
+// = N keeps the first N entries of every lane's stack in shared memory instead ([entry][thread], conflict-free,
+// one wavefront per access); deeper entries stay in local memory.  Blocks of at most 128 threads.
+#ifndef MCPT_SHARED_STACK
+#define MCPT_SHARED_STACK 0
+#endif
+#ifndef MCPT_SELECT_PREDICATED
+#define MCPT_SELECT_PREDICATED 1
+#endif
+#if MCPT_SHARED_STACK
+#define MCPT_STACK_DECL __shared__ int sstack_[MCPT_SHARED_STACK * 128]; int* const sst_ = sstack_ + threadIdx.x;
+#define MCPT_PUSH(v) do { if (sp < MCPT_SHARED_STACK) sst_[sp * 128] = (v); else w.stack[sp] = (v); ++sp; } while (0)
+#define MCPT_POP() (--sp, sp < MCPT_SHARED_STACK ? sst_[sp * 128] : w.stack[sp])
+#else
+#define MCPT_STACK_DECL
+#define MCPT_PUSH(v) (w.stack[sp++] = (v))
+#define MCPT_POP() (w.stack[--sp])
+#endif
+
 template <bool COUNT>
 __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const RayRegs& ray, float tmin) {
+	MCPT_STACK_DECL
 	const float rx = w.rx, ry = w.ry, rz = w.rz;
 	int cur = w.cur, sp = w.sp, pending = w.pending;
 	float best = w.best;
@@ -555,25 +576,40 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		int cl_ = link.x < 0 ? (LEAF_FLAG | ~link.x) : link.x;
 		int cr_ = link.y < 0 ? (LEAF_FLAG | ~link.y) : link.y;
 #endif
+#if MCPT_SELECT_PREDICATED
+		// one straight-line selection instead of four divergent arms (ncu r1n: the arms ran at 11 of 32 lanes)
+		{
+			const bool swap = loR < loL, both = hitL && hitR;
+			const int nearc = (hitL && !(hitR && swap)) ? cl_ : cr_;
+			if (both) MCPT_PUSH(swap ? cl_ : cr_);
+			int nxt = nearc;
+			if (!(hitL || hitR)) {
+				nxt = WALK_DONE;
+				if (sp > 0) nxt = MCPT_POP();
+			}
+			cur = nxt;
+		}
+#else
 		if (hitL && hitR) {
 			const bool swap = loR < loL;
 			const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
-			w.stack[sp++] = farc;      // cannot overflow: mcpt_upload_scene checks the depth of the fast tree against STACK_SIZE
+			MCPT_PUSH(farc);           // cannot overflow: mcpt_upload_scene checks the depth of the fast tree against STACK_SIZE
 			cur = nearc;
 		} else if (hitL) cur = cl_;
 		else if (hitR) cur = cr_;
-		else cur = sp > 0 ? w.stack[--sp] : WALK_DONE;
+		else cur = sp > 0 ? MCPT_POP() : WALK_DONE;
+#endif
 #if MCPT_POSTPONE_LEAF
 		// the first leaf found is postponed so that the lane keeps traversing while its warp mates still
 		// search: candidates need not arrive in any particular order (see the replay argument above)
-		if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? w.stack[--sp] : WALK_DONE; }
+		if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? MCPT_POP() : WALK_DONE; }
 #endif
 	}
 	// ---- leaves: certified reference box test, then the certified triangle test
 	while (pending != 0 || cur < 0) {
 		int leaf;
 		if (pending != 0) { leaf = pending; pending = 0; }
-		else { leaf = cur; cur = sp > 0 ? w.stack[--sp] : WALK_DONE; }
+		else { leaf = cur; cur = sp > 0 ? MCPT_POP() : WALK_DONE; }
 		const int tri = leaf & 0x7fffffff;
 		const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
 		float4 q0, q1;

@@ -27,7 +27,7 @@ EXPORTS = [
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
-    "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics",
+    "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
 ]
 
 
@@ -176,6 +176,11 @@ class Context:
         r = np.ascontiguousarray(rays, dtype=T.RAY)
         assert len(r) == self.npix
         self._call("mcpt_write_rays", _vp(r))
+
+    def merge_sums(self, others):
+        """sums += the other contexts' sums (in order), on the device over peer memory (mcpt_merge_sums)."""
+        arr = (ctypes.c_void_p * max(1, len(others)))(*[o._h for o in others])
+        self._call("mcpt_merge_sums", arr, len(others))
 
     def read_hits(self):
         hits = np.zeros(self.npix, T.HIT)

@@ -247,6 +247,34 @@ def test_sample_sharding_merges_exactly(cbox):
     np.testing.assert_allclose(m, s, rtol=1e-12)
 
 
+def test_device_merge_equals_host_merge(cbox):
+    """mcpt_merge_sums (one kernel reading the other contexts' accumulators in place; NVLink peer mappings across
+    devices) gives the doubles of a host-side merge in context order."""
+    w = h = 64
+    parts = []
+    ctxs = [_ctx(cbox, w, h, seed_mode=1, run_seed=3, samples_in_flight=2) for _ in range(3)]
+    try:
+        for k, c in enumerate(ctxs):
+            c.set_first_sample(4 * k)
+            c.render(4)
+            parts.append(c.read_sums())
+        want = parts[0].copy()
+        for p in parts[1:]:
+            want += p
+        ctxs[0].merge_sums(ctxs[1:])
+        got = ctxs[0].read_sums()
+        assert got.tobytes() == want.tobytes()
+        assert got[6].sum() > 0
+        assert np.array_equal(ctxs[1].read_sums(), parts[1])          # sources untouched
+        ctxs[0].merge_sums([])                                          # nothing to add
+        assert ctxs[0].read_sums().tobytes() == want.tobytes()
+        with pytest.raises(device.McptError):
+            ctxs[0].merge_sums([ctxs[0]])
+    finally:
+        for c in ctxs:
+            c.close()
+
+
 def test_error_paths(cbox):
     with pytest.raises(device.McptError):
         device.Context(0, 10, 8, 1)
