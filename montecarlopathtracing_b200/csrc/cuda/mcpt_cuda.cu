@@ -1,5 +1,6 @@
 // libmcpt_cuda.so — context management and the C ABI of include/mcpt.h (sm_100a only, no CPU fallback).
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -7,6 +8,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "mcpt.h"
@@ -467,6 +469,24 @@ static int build_emitters(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, con
 	return MCPT_OK;
 }
 
+// memcmp(a, b, n) == 0 on up to 8 threads: the cache checks below compare ~80 MB per upload, which one core does
+// in about 10 ms - as long as the copies they save.
+static bool bytes_equal(const void* a, const void* b, size_t n) {
+	const size_t chunk = size_t(4) << 20;
+	if (n < 2 * chunk) return std::memcmp(a, b, n) == 0;
+	const unsigned nt = unsigned(std::min<size_t>(8, (n + chunk - 1) / chunk));
+	std::atomic<bool> same{true};
+	std::vector<std::thread> th;
+	for (unsigned t = 0; t < nt; ++t) {
+		const size_t lo = n * t / nt, hi = n * (t + 1) / nt;
+		th.emplace_back([&, lo, hi] {
+			if (std::memcmp(static_cast<const char*>(a) + lo, static_cast<const char*>(b) + lo, hi - lo) != 0) same = false;
+		});
+	}
+	for (auto& x : th) x.join();
+	return same;
+}
+
 // Everything mcpt_upload_scene derives from the geometry alone (leaf records, two-box nodes of the reference
 // topology, the binned-SAH tree of the fast walk).  Kept per process for the last scene, so that the N contexts of
 // a multi-GPU run derive it once (the SAH build is the expensive part of an upload).
@@ -589,8 +609,8 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
 	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
 	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
-	    std::memcmp(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
-	    std::memcmp(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
+	    bytes_equal(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
+	    bytes_equal(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)) {
 		for (int m = 0; m < nmats; ++m)
 			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
 				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
@@ -611,8 +631,8 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	{
 		std::lock_guard<std::mutex> lock(g_derived_mutex);
 		if (g_derived && g_derived->nmats == nmats && g_derived->tris.size() == size_t(ntris) && g_derived->nodes.size() == size_t(nnodes) &&
-		    std::memcmp(g_derived->tris.data(), tris, sizeof(mcpt_triangle) * ntris) == 0 &&
-		    std::memcmp(g_derived->nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes) == 0) {
+		    bytes_equal(g_derived->tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
+		    bytes_equal(g_derived->nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)) {
 			derived = g_derived;
 		} else {
 			auto fresh = std::make_shared<DerivedScene>();

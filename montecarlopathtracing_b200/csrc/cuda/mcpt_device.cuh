@@ -219,10 +219,19 @@ __device__ __forceinline__ MaterialDev load_material(const mcpt_material* __rest
 	return m;
 }
 
+// The Phong lobe's pow (shade.cl:143) is a double-precision subroutine that a handful of lanes per warp need
+// (ncu r1n: 27% of the shade kernel's instructions at 2-4 of 32 lanes).  With `defer`, shade_one leaves that one
+// factor open: colour holds colour * ks, the arguments and the trailing factor go to *defer, and the caller finishes
+// with finish_phong() once it has evaluated the pows of a whole block in dense warps.  Same operations, same order.
+struct PhongDefer { float x, y, post; bool pending; };
+__device__ __forceinline__ void finish_phong(f4& color, float p, float post) { color = color * p * post / TWO_PI_F; }
+
 __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
                                           RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
-                                          uint32_t& seed_slot, int max_depth, bool* diffuse_lobe = nullptr) {
+                                          uint32_t& seed_slot, int max_depth, bool* diffuse_lobe = nullptr,
+                                          PhongDefer* defer = nullptr) {
 	if (diffuse_lobe) *diffuse_lobe = false;
+	if (defer) defer->pending = false;
 	const uint32_t state = uint32_t(__float_as_int(ray.origin.w));
 	if (hit_t >= FLT_MAX) {                                                   // :92-96
 		color = f4{0, 0, 0, 0};
@@ -246,7 +255,10 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		} while (specular && dot3(new_dir, n) <= 0);
 		new_org = ip + KERNEL_EPSILON * new_dir;
 		new_state = int32_t(state) + 1;
-		if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
+		if (specular && defer) {
+			color = color * mat.ka_ks;
+			defer->x = dot3(new_dir, axis); defer->y = mat.Ns; defer->post = dot3(new_dir, n); defer->pending = true;
+		} else if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
 		else color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
 		if (diffuse_lobe) *diffuse_lobe = !specular;
 		seed_slot = seed;
@@ -285,6 +297,7 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		color = f4{0, 0, 0, 0};
 		new_state = int32_t(uint32_t(new_state) | MCPT_RAY_TERM_MASK);
 		alive = false;
+		if (defer) defer->pending = false;                                     // the colour is already final (zero)
 	}
 	const float pixel_w = ray.direction.w;
 	ray.origin = f4{new_org.x, new_org.y, new_org.z, __int_as_float(new_state)};

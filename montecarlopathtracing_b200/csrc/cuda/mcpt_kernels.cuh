@@ -289,6 +289,9 @@ namespace mcpt {
 #ifndef MCPT_SHADE_BINS
 #define MCPT_SHADE_BINS 0        // 8: direction-octant grouping of the next queue inside each shading block - measured -1.6% (the origins stay incoherent)
 #endif
+#ifndef MCPT_DENSE_POW
+#define MCPT_DENSE_POW 1         // k_wave_shade: the block's Phong pows are gathered and evaluated by full warps
+#endif
 #ifndef MCPT_REFILL_THRESHOLD
 #define MCPT_REFILL_THRESHOLD 22
 #endif
@@ -466,13 +469,20 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 #if MCPT_SHADE_BINS
 	__shared__ uint32_t bin_count[MCPT_SHADE_BINS], bin_base[MCPT_SHADE_BINS];
 #endif
+#if MCPT_DENSE_POW
+	__shared__ float pow_x[256], pow_y[256];
+	__shared__ uint32_t pow_count;
+#endif
 	for (uint32_t bbase = blockIdx.x * blockDim.x; bbase < total; bbase += stride) {   // block-uniform trip count
 		const uint32_t i = bbase + threadIdx.x;
-		bool alive = false;
+		bool alive = false, finished = false;
 		RayRegs ray;
 		f4 color{0, 0, 0, 0};
 		uint32_t seed = 0;
 		int path = 0;
+#if MCPT_DENSE_POW
+		PhongDefer defer{0.0f, 0.0f, 0.0f, false};
+#endif
 		if (i < total) {
 			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
 			const float2 hr = __ldcs(w.hitrec + i);
@@ -494,11 +504,31 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 				ip = ray.origin + t * ray.direction;
 				if (dot3(ray.direction, nn) > 0) nn = -nn;
 			}
+#if MCPT_DENSE_POW
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, nullptr, &defer);
+#else
 			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth);
-			if (!alive) {
-				__stcs(w.sample_out + path, make_float4(color.x, color.y, color.z, 0.0f));
-				if (seed_mode == 0) w.seeds[pixel] = seed;
-			}
+#endif
+			finished = !alive;
+		}
+#if MCPT_DENSE_POW
+		// the block's Phong pows, gathered and evaluated by full warps (see PhongDefer)
+		if (threadIdx.x == 0) pow_count = 0u;
+		__syncthreads();
+		uint32_t slot = 0;
+		if (defer.pending) {
+			slot = atomicAdd(&pow_count, 1u);
+			pow_x[slot] = defer.x;
+			pow_y[slot] = defer.y;
+		}
+		__syncthreads();
+		if (threadIdx.x < pow_count) pow_x[threadIdx.x] = cr_pow(pow_x[threadIdx.x], pow_y[threadIdx.x]);
+		__syncthreads();
+		if (defer.pending) finish_phong(color, pow_x[slot], defer.post);
+#endif
+		if (finished) {
+			__stcs(w.sample_out + path, make_float4(color.x, color.y, color.z, 0.0f));
+			if (seed_mode == 0) w.seeds[path % w.npix] = seed;
 		}
 #if MCPT_SHADE_BINS
 		// The block's survivors enter the next queue grouped by direction octant (a counting sort in shared
