@@ -290,7 +290,9 @@ namespace mcpt {
 #define MCPT_SHADE_BINS 0        // 8: direction-octant grouping of the next queue inside each shading block - measured -1.6% (the origins stay incoherent)
 #endif
 #ifndef MCPT_DENSE_POW
-#define MCPT_DENSE_POW 1         // k_wave_shade: the block's Phong pows are gathered and evaluated by full warps
+#define MCPT_DENSE_POW 0         // 1: k_wave_shade gathers the block's Phong pows and evaluates them in full warps.
+                                 // Bit-identical; measured -1.5% on the loop (three block barriers per batch cost
+                                 // more than the pow's 27% of instructions at 2-4 lanes save), so it is off.
 #endif
 #ifndef MCPT_REFILL_THRESHOLD
 #define MCPT_REFILL_THRESHOLD 22
