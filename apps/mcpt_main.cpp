@@ -17,6 +17,8 @@
 #include <cstring>
 #include <string>
 #include <thread>
+#include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "mcpt.h"
@@ -38,6 +40,8 @@ struct State {
 	bool reference_seeding = true;
 	bool mis = false;        // --mis: NEE + MIS sampling mode (same image, far less variance; needs order-independent seeds)
 	bool host_bvh = false;   // --host-bvh: build the LBVH with the kept host code instead of the device builder
+	bool overlap_init = false;   // --overlap-init (multi-GPU): every device starts rendering as soon as IT is ready
+	double first_ready_s = 0.0, all_ready_s = 0.0;
 };
 
 [[noreturn]] void die(const char* what, const char* detail) {
@@ -76,6 +80,25 @@ void test_model(const mcpt_host_config& cfg, const char* objname, bool with_came
 	mcpt_host_free(ids);
 }
 
+mcpt_ctx* make_context(const State& s, int g, int ngpus) {
+	mcpt_params p{};
+	p.width = s.cfg.width;
+	p.height = s.cfg.height;
+	p.max_depth = s.cfg.maxdepth;
+	p.max_attempt = s.cfg.attempt;
+	p.device = g;
+	p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
+	p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
+	p.run_seed = s.run_seed;
+	p.traversal = MCPT_TRAVERSAL_FAST;
+	mcpt_ctx* c = mcpt_create(&p);
+	if (!c) die("mcpt_create", mcpt_last_error());
+	if (mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size())) ||
+	    mcpt_set_camera(c, &s.cfg.camera))
+		die("scene upload", mcpt_last_error());
+	return c;
+}
+
 void init(State& s, int ngpus) {
 	if (!s.cfg.opencl) die("config", "Not Implemented");            // raygeneration.cpp:36-38 throws the same
 	if (mcpt_host_load_object_mt(s.cfg.directory, s.cfg.objname, 1, 0, &s.tris, &s.ntris, &s.mats, &s.nmats, &s.mat_ids) < 0)
@@ -95,27 +118,9 @@ void init(State& s, int ngpus) {
 	// one host thread per device: context creation, buffers and uploads overlap; the geometry-derived layout
 	// (SAH tree of the fast walk) is built by the first thread and shared through the library's per-process cache
 	s.ctx.assign(size_t(ngpus), nullptr);
+	if (s.overlap_init) return;                                     // run_overlapped() creates them
 	std::vector<std::thread> th;
-	for (int g = 0; g < ngpus; ++g) {
-		th.emplace_back([&s, g, ngpus] {
-			mcpt_params p{};
-			p.width = s.cfg.width;
-			p.height = s.cfg.height;
-			p.max_depth = s.cfg.maxdepth;
-			p.max_attempt = s.cfg.attempt;
-			p.device = g;
-			p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
-			p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
-			p.run_seed = s.run_seed;
-			p.traversal = MCPT_TRAVERSAL_FAST;
-			mcpt_ctx* c = mcpt_create(&p);
-			if (!c) die("mcpt_create", mcpt_last_error());
-			if (mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size())) ||
-			    mcpt_set_camera(c, &s.cfg.camera))
-				die("scene upload", mcpt_last_error());
-			s.ctx[size_t(g)] = c;
-		});
-	}
+	for (int g = 0; g < ngpus; ++g) th.emplace_back([&s, g, ngpus] { s.ctx[size_t(g)] = make_context(s, g, ngpus); });
 	for (auto& t : th) t.join();
 }
 
@@ -133,6 +138,34 @@ void update(State& s, int first_frame, int frames) {
 		});
 	}
 	for (auto& t : th) t.join();
+}
+
+// --overlap-init: CUDA brings the devices of a process up one after the other (about a second each on an 8-GPU
+// box), so with a static split everybody waits for the last one.  Here each device's thread creates its context and
+// then pulls blocks of sample indices from a shared counter until none are left: the device that is ready first
+// renders most.  Same samples, same sums (seed_mode 1 makes a sample a function of its index alone).
+void run_overlapped(State& s, int frames, int batch, std::chrono::steady_clock::time_point t0) {
+	const int G = int(s.ctx.size());
+	std::atomic<int> next{0};
+	std::vector<double> ready(size_t(G), 0.0);
+	std::vector<std::thread> th;
+	for (int g = 0; g < G; ++g) {
+		th.emplace_back([&, g] {
+			mcpt_ctx* c = make_context(s, g, G);
+			s.ctx[size_t(g)] = c;
+			ready[size_t(g)] = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+			for (;;) {
+				const int first = next.fetch_add(batch);
+				if (first >= frames) break;
+				const int count = std::min(batch, frames - first);
+				if (mcpt_set_first_sample(c, uint32_t(first))) die("mcpt_set_first_sample", mcpt_last_error());
+				if (mcpt_render(c, count)) die("mcpt_render", mcpt_last_error());
+			}
+		});
+	}
+	for (auto& t : th) t.join();
+	s.first_ready_s = *std::min_element(ready.begin(), ready.end());
+	s.all_ready_s = *std::max_element(ready.begin(), ready.end());
 }
 
 }  // namespace App
@@ -156,7 +189,8 @@ int main(int argc, char** argv) {
 		else if (a == "--order-independent-seeds") s.reference_seeding = false;
 		else if (a == "--host-bvh") s.host_bvh = true;
 		else if (a == "--mis") s.mis = true;
-		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch --order-independent-seeds --host-bvh --mis)", a.c_str());
+		else if (a == "--overlap-init") s.overlap_init = true;
+		else die("unknown option (use --config --configid --gpus --spp --out --seed --batch --order-independent-seeds --host-bvh --mis --overlap-init)", a.c_str());
 	}
 	if (mcpt_host_load_config(config.c_str(), configid, &s.cfg) < 0) die("config", mcpt_host_last_error());
 	if (s.cfg.testall) {                                     // main.cpp:12-15 -> BVH::TEST::testall(), bvhtest.cpp:615-650
@@ -172,15 +206,20 @@ int main(int argc, char** argv) {
 	}
 	if (spp_override >= 0) s.cfg.attempt = spp_override;
 	if (gpus < 1) gpus = 1;
+	if (gpus == 1) s.overlap_init = false;
 	auto t0 = std::chrono::steady_clock::now();
 	init(s, gpus);
 	auto t1 = std::chrono::steady_clock::now();
 	// the reference accumulates while attemptCount <= attempt, i.e. attempt + 1 frames (colorout.cpp:55-62)
 	const int frames = s.cfg.attempt + 1;
-	for (int done = 0; done < frames;) {
-		int n = std::min(batch * gpus, frames - done);
-		update(s, done, n);
-		done += n;
+	if (s.overlap_init) {
+		run_overlapped(s, frames, std::min(batch, 32), t0);
+	} else {
+		for (int done = 0; done < frames;) {
+			int n = std::min(batch * gpus, frames - done);
+			update(s, done, n);
+			done += n;
+		}
 	}
 	auto t2 = std::chrono::steady_clock::now();
 	const size_t npix = size_t(s.cfg.width) * size_t(s.cfg.height);
@@ -213,9 +252,11 @@ int main(int argc, char** argv) {
 	double sec = std::chrono::duration<double>(t2 - t1).count();
 	std::printf("Finished Attempting\n");                                    // colorout.cpp:65
 	std::printf("{\"scene\": \"%s%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"gpus\": %d, \"init_s\": %.3f, "
-	            "\"render_s\": %.3f, \"merge_read_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
+	            "\"render_s\": %.3f, \"merge_read_s\": %.3f, \"total_s\": %.3f, \"first_gpu_ready_s\": %.3f, \"all_gpus_ready_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
 	            s.cfg.directory, s.cfg.objname, s.cfg.width, s.cfg.height, frames, gpus,
-	            std::chrono::duration<double>(t1 - t0).count(), sec, std::chrono::duration<double>(t3 - t2).count(), tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
+	            std::chrono::duration<double>(t1 - t0).count(), sec, std::chrono::duration<double>(t3 - t2).count(), std::chrono::duration<double>(t3 - t0).count(),
+	            s.overlap_init ? s.first_ready_s : std::chrono::duration<double>(t1 - t0).count(),
+	            s.overlap_init ? s.all_ready_s : std::chrono::duration<double>(t1 - t0).count(), tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
 	for (mcpt_ctx* c : s.ctx) mcpt_destroy(c);
 	mcpt_host_free(s.tris);
 	mcpt_host_free(s.mats);
