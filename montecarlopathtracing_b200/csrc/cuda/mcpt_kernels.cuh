@@ -248,11 +248,21 @@ __global__ void __launch_bounds__(256) k_wave_resolve(WaveDev w, int nsamples, i
 	if (p >= w.npix) return;
 	f4 h = ld4(w.hist[p]);
 	int32_t cnt = w.counts[p];
+	// The running sums continue from their stored values, one sample at a time: ((prev + x1) + x2) + ..., so the
+	// doubles do not depend on how a render is cut into waves (and equal a frame-by-frame accumulation).
+	const size_t n = size_t(w.npix);
 	double s0 = 0, s1 = 0, s2 = 0, q0 = 0, q1 = 0, q2 = 0, k = 0;
+	bool touched = false;
 	for (int s = 0; s < nsamples; ++s) {
 		f4 c = ld4(w.sample_out[size_t(s) * w.npix + p]);
 		f4 raw = c;
 		if (history_one(c, h, cnt, max_attempt)) {
+			if (!touched) {
+				s0 = w.sums[p]; s1 = w.sums[n + p]; s2 = w.sums[2 * n + p];
+				q0 = w.sums[3 * n + p]; q1 = w.sums[4 * n + p]; q2 = w.sums[5 * n + p];
+				k = w.sums[6 * n + p];
+				touched = true;
+			}
 			s0 += raw.x; s1 += raw.y; s2 += raw.z;
 			q0 += double(raw.x) * raw.x; q1 += double(raw.y) * raw.y; q2 += double(raw.z) * raw.z;
 			k += 1.0;
@@ -260,11 +270,10 @@ __global__ void __launch_bounds__(256) k_wave_resolve(WaveDev w, int nsamples, i
 	}
 	w.hist[p] = st4(h);
 	w.counts[p] = cnt;
-	if (k > 0) {
-		const size_t n = size_t(w.npix);
-		w.sums[p] += s0; w.sums[n + p] += s1; w.sums[2 * n + p] += s2;
-		w.sums[3 * n + p] += q0; w.sums[4 * n + p] += q1; w.sums[5 * n + p] += q2;
-		w.sums[6 * n + p] += k;
+	if (touched) {
+		w.sums[p] = s0; w.sums[n + p] = s1; w.sums[2 * n + p] = s2;
+		w.sums[3 * n + p] = q0; w.sums[4 * n + p] = q1; w.sums[5 * n + p] = q2;
+		w.sums[6 * n + p] = k;
 	}
 }
 

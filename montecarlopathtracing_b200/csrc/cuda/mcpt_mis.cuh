@@ -217,17 +217,19 @@ __global__ void __launch_bounds__(256) k_wave_resolve_mis(WaveDev w, MisDev m, i
 		*w.first_sample += uint32_t(nsamples);
 	}
 	if (p >= w.npix) return;
-	double s0 = 0, s1 = 0, s2 = 0, q0 = 0, q1 = 0, q2 = 0, k = 0;
+	// continue from the stored sums one sample at a time: independent of the wave split (see k_wave_resolve)
+	const size_t n = size_t(w.npix);
+	double s0 = w.sums[p], s1 = w.sums[n + p], s2 = w.sums[2 * n + p];
+	double q0 = w.sums[3 * n + p], q1 = w.sums[4 * n + p], q2 = w.sums[5 * n + p], k = w.sums[6 * n + p];
 	for (int s = 0; s < nsamples; ++s) {
 		const float4 c = w.sample_out[size_t(s) * w.npix + p];
 		s0 += c.x; s1 += c.y; s2 += c.z;
 		q0 += double(c.x) * c.x; q1 += double(c.y) * c.y; q2 += double(c.z) * c.z;
 		k += c.w;
 	}
-	const size_t n = size_t(w.npix);
-	w.sums[p] += s0; w.sums[n + p] += s1; w.sums[2 * n + p] += s2;
-	w.sums[3 * n + p] += q0; w.sums[4 * n + p] += q1; w.sums[5 * n + p] += q2;
-	w.sums[6 * n + p] += k;
+	w.sums[p] = s0; w.sums[n + p] = s1; w.sums[2 * n + p] = s2;
+	w.sums[3 * n + p] = q0; w.sums[4 * n + p] = q1; w.sums[5 * n + p] = q2;
+	w.sums[6 * n + p] = k;
 }
 
 }  // namespace mcpt
