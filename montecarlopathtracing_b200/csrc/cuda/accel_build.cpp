@@ -35,7 +35,10 @@ struct Box {
 	}
 };
 
-constexpr int BINS = 16;
+#ifndef MCPT_SAH_BINS
+#define MCPT_SAH_BINS 16
+#endif
+constexpr int BINS = MCPT_SAH_BINS;
 constexpr int MAX_SAH_DEPTH = 40;        // below this depth: median splits, so the traversal stack (64) cannot overflow
 
 struct Builder {
