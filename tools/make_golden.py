@@ -5,11 +5,16 @@ What each fixture pins:
   bvh_digests.npz   sha256 of the BVHNode[] the REFERENCE's own BVH/hlbvh.cpp (compiled into
                     oracle/_ref) builds for assets/cbox and assets/veach_mis, and of the Triangle[] /
                     Material[] its loadObject produces -> pins our host layer to reference outputs.
-  cbox_primary.npz  oracle closest-hit records for the cbox camera at 48x48 (t bits, ids, materials)
+  cbox_primary.npz  closest-hit records for the cbox camera at 48x48 (t bits, ids, materials), produced by the
+                    REFERENCE'S OWN kernels (kernels/rayGenerator.cl + intersect.cl compiled as C++ into
+                    oracle/_ref/libmcpt_refcl.so) and asserted equal to the oracle's; `closest` and the fetch
+                    counters come from the oracle (the kernels do not report them)
   mis_primary.npz   same for veach_mis at 64x36
-  cbox_render.npz   oracle render 24x24, 6 frames, depth 8, cap 5, both seed modes (running mean + counts)
-The kernel restatement itself is "parity unpinned" by the reference (it has no tests and its OpenCL
-kernels cannot run here); these files pin the oracle against regressions and travel to the GPU box.
+  cbox_render.npz   render 24x24, 6 frames, depth 8, cap 5: seed mode 0 (one LCG stream per pixel, as the reference)
+                    from the reference's kernels driven like OpenCL::update and asserted equal to oracle_render;
+                    seed mode 1 (order-independent samples, an extension) from the oracle
+The reference ships no tests or golden vectors of its own; these are outputs of its code run here.  They travel to
+the GPU box, where /root/reference does not exist.
 """
 import ctypes
 import hashlib
@@ -62,8 +67,11 @@ def main():
     np.savez(os.path.join(OUT, "bvh_digests.npz"), **{k: np.array(v) for k, v in dig.items()})
     for name, (w, h) in (("cbox", (48, 48)), ("veach_mis", (64, 36))):
         sc = scenes.load(name)
-        rays = O.generate_rays(sc.camera, w, h)
-        hits, closest, cnt = O.intersect(rays, sc.nodes, sc.triangles, count=True)
+        rays = O.refcl_generate_rays(sc.camera, w, h)
+        assert rays.tobytes() == O.generate_rays(sc.camera, w, h).tobytes()
+        hits = O.refcl_intersect(rays.copy(), sc.nodes, sc.triangles)
+        o_hits, closest, cnt = O.intersect(rays, sc.nodes, sc.triangles, count=True)
+        assert hits.tobytes() == o_hits.tobytes()
         np.savez_compressed(os.path.join(OUT, ("cbox" if name == "cbox" else "mis") + "_primary.npz"),
                             width=w, height=h, rays_sha=np.array(sha(rays)), closest=closest,
                             t_bits=hits["t"].view(np.uint32), material=hits["material_id"], raw_id=hits["triangle_id"],
@@ -73,6 +81,12 @@ def main():
     out = {}
     for mode in (0, 1):
         r = O.render(sc.camera, 24, 24, sc.nodes, sc.triangles, sc.materials, 8, 5, 6, seed_mode=mode, run_seed=11)
+        if mode == 0:
+            seeds = O.init_seeds(24 * 24, 11)
+            hist, counts = np.zeros((24 * 24, 4), np.float32), np.zeros(24 * 24, np.int32)
+            traced = O.refcl_update(sc.camera, 24, 24, sc.nodes, sc.triangles, sc.materials, 8, 5, 6, seeds, hist, counts)
+            assert hist.tobytes() == r["hist"].tobytes() and np.array_equal(counts, r["counts"]) and traced == r["rays_traced"]
+            r = {"hist": hist, "counts": counts, "rays_traced": traced}
         out["hist_bits_%d" % mode] = r["hist"].view(np.uint32)
         out["counts_%d" % mode] = r["counts"]
         out["rays_%d" % mode] = np.array(r["rays_traced"])
