@@ -215,6 +215,8 @@ int main(int argc, char** argv) {
 	if (s.overlap_init) {
 		run_overlapped(s, frames, std::min(batch, 32), t0);
 	} else {
+		// one device: one call (seed_mode 0 regenerates paths inside the library and wants the whole run at once)
+		if (gpus == 1) batch = frames;
 		for (int done = 0; done < frames;) {
 			int n = std::min(batch * gpus, frames - done);
 			update(s, done, n);

@@ -110,6 +110,8 @@ struct mcpt_ctx {
 		m.emit_tri = emit_tri.p; m.emit_cdf = emit_cdf.p; m.nemit = nemit; m.emit_area = emit_area;
 		return m;
 	}
+	DevBuf<uint32_t> rq_count, rq_head;    // per-round counter rings of the regeneration loop (seed_mode 0)
+	DevBuf<int32_t> frames_left;
 	DevBuf<uint32_t> qcount, qhead, first_sample;   // qhead[d]: work-fetch cursor of the persistent bounce d (+1 slot for mcpt_trace)
 	int nsm = 148;
 	DevBuf<unsigned long long> counters;   // 0 nodes, 1 tris, 2 live rays (stage path), 3 rays (wave), 4 paths (wave)
@@ -281,6 +283,60 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	}
 	k_wave_resolve<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, nsamples, D, c->prm.max_attempt);
 	c->launches += uint64_t(D) + 2;
+	CU(cudaGetLastError());
+	return MCPT_OK;
+}
+
+// seed_mode 0, `frames` more samples of every pixel with path regeneration (k_wave_shade_regen): rounds of
+// (walk, shade + fold + regenerate) until no pixel has samples left.  The host cannot know the number of rounds (it
+// is the longest chain of path lengths of any pixel), so rounds are enqueued in chunks and the live count is read
+// back after each chunk; rounds past the end find an empty queue and return at once.
+#ifndef MCPT_REGEN_DEFAULT
+#define MCPT_REGEN_DEFAULT 0
+#endif
+constexpr int REGEN_CHUNK = 1024;      // even: the queue parity carries over from chunk to chunk
+
+int enqueue_regen(mcpt_ctx* c, int frames) {
+	const int D = c->prm.max_depth;
+	const int n = c->npix;
+	if (int r = ensure_wave(c, 1)) return r;
+	CU(c->rq_count.alloc(REGEN_CHUNK + 2));
+	CU(c->rq_head.alloc(REGEN_CHUNK + 2));
+	CU(c->frames_left.alloc(size_t(n)));
+	WaveDev w = c->wave();
+	w.qcount = c->rq_count.p;
+	const int BS = c->block;
+	const int g = blocks(n, BS);
+	k_fill_i32<<<blocks(n, 256), 256, 0, c->stream>>>(c->frames_left.p, n, frames);
+	CU(cudaMemsetAsync(c->rq_count.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
+	CU(cudaMemsetAsync(c->rq_head.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
+	k_wave_generate<<<blocks(n, 256), 256, 0, c->stream>>>(c->cam, w, 1, 0, c->prm.run_seed);      // sample 1 of every pixel -> queue 0
+	c->launches += 2;
+	const long max_rounds = long(frames) * D;        // every path ends within D rounds of its start
+	long done_rounds = 0;
+	uint32_t live = uint32_t(n);
+	while (live > 0 && done_rounds < max_rounds) {
+		// a chunk no longer than what the live paths can still need at most, rounded up to an even count
+		long want = std::min<long>(REGEN_CHUNK, max_rounds - done_rounds);
+		const int rounds = int((want + 1) & ~1L);
+		for (int r = 0; r < rounds; ++r) {
+			k_wave_trace_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, r, c->prm.tmin, c->rq_head.p + r);
+			k_wave_shade_regen<<<std::min(blocks(n, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, c->cam, r, D, c->prm.max_attempt, c->frames_left.p);
+		}
+		c->launches += 2 * uint64_t(rounds);
+		CU(cudaMemcpyAsync(&live, c->rq_count.p + rounds, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+		// carry the queue over: round `rounds` of this chunk is round 0 of the next (same parity, rounds is even)
+		CU(cudaMemcpyAsync(c->rq_count.p, c->rq_count.p + rounds, sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+		CU(cudaMemsetAsync(c->rq_count.p + 1, 0, sizeof(uint32_t) * (REGEN_CHUNK + 1), c->stream));
+		CU(cudaMemsetAsync(c->rq_head.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
+		CU(cudaStreamSynchronize(c->stream));
+		done_rounds += rounds;
+	}
+	if (live != 0) return fail(MCPT_ERR_STATE, "mcpt_render: regeneration loop did not drain (internal error)");
+	// bookkeeping the frame loop does in k_wave_resolve
+	const unsigned long long paths = (unsigned long long)frames * (unsigned long long)n;
+	k_add_stats<<<1, 1, 0, c->stream>>>(w.paths_done, paths, w.first_sample, uint32_t(frames));
+	++c->launches;
 	CU(cudaGetLastError());
 	return MCPT_OK;
 }
@@ -839,6 +895,12 @@ int mcpt_render_async(mcpt_ctx* c, int spp) {
 		if (S < 1) S = 1;
 		if (S > 64) S = 64;
 	}
+	// seed_mode 0 with the product walk: path regeneration instead of one wave per frame (MCPT_REGEN_DEFAULT; MCPT_OPT
+	// bit 16 selects the other one)
+	if (c->prm.seed_mode == 0 && spp >= 2 && c->prm.sampling == MCPT_SAMPLING_REFERENCE && !(c->opt_flags & (2 | 8)) &&
+	    (((c->opt_flags & 16) != 0) != (MCPT_REGEN_DEFAULT != 0)) &&
+	    c->traversal(c->prm.traversal) == MCPT_TRAVERSAL_FAST && !c->count_fetches && !c->time_bounces)
+		return enqueue_regen(c, spp);
 	if (S > spp && spp > 0) S = spp;
 	if (int r = ensure_wave(c, S)) return r;
 	for (int done = 0; done < spp;) {

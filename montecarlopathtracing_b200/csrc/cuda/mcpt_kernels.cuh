@@ -592,6 +592,97 @@ __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_bounce_persistent
 	persistent_walk(sc, tmin, total, head, job);
 }
 
+// ---- path regeneration for seed_mode 0 (one LCG stream per pixel, continued from sample to sample, shade.cl:101).
+// A pixel's samples are sequential by construction, so a frame-at-a-time wave has one sample of every pixel in flight
+// and its late bounces run almost empty (cbox 1024^2: 1 M rays at bounce 0, 0.4 M at bounce 7).  Here a pixel whose
+// path ends folds the sample into hist / counts / sums at once (history.cl's update, the same per-pixel order) and
+// starts its next sample in the same launch, so every round traces one ray per unfinished pixel, whatever the
+// depths of the individual paths.  Round r reads queue r & 1 and writes queue (r + 1) & 1; qcount is a ring of
+// per-round counters prepared by the host.  Results are those of the frame loop bit for bit.
+__global__ void __launch_bounds__(256) k_wave_shade_regen(SceneDev sc, WaveDev w, CameraDev cam, int round, int max_depth, int max_attempt,
+                                                          int32_t* __restrict__ frames_left) {
+	const int src = round & 1, dst = src ^ 1;
+	const uint32_t total = w.qcount[round];
+	const unsigned lane = threadIdx.x & 31u;
+	const uint32_t stride = gridDim.x * blockDim.x;
+	if (blockIdx.x == 0 && threadIdx.x == 0) *w.rays_traced += total;
+	const size_t n = size_t(w.npix);
+	for (uint32_t bbase = blockIdx.x * blockDim.x; bbase < total; bbase += stride) {   // block-uniform trip count
+		const uint32_t i = bbase + threadIdx.x;
+		bool alive = false;
+		RayRegs ray;
+		f4 color{0, 0, 0, 0};
+		uint32_t seed = 0;
+		int pixel = 0;
+		if (i < total) {
+			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
+			const float2 hr = __ldcs(w.hitrec + i);
+			const float t = hr.x;
+			const int closest = __float_as_int(hr.y);
+			pixel = __float_as_int(d.w);
+			ray.origin = ld4(o);
+			ray.direction = f4{d.x, d.y, d.z, __int_as_float(pixel)};
+			color = f4{c.x, c.y, c.z, 0.0f};
+			seed = uint32_t(__float_as_int(c.w));
+			f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
+			uint32_t mat = 0;
+			if (closest >= 0) {
+				const float4* tp = reinterpret_cast<const float4*>(sc.leaves + closest);
+				float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+				nn = f4{q2.w, q3.w, q4.w, 0.0f};
+				mat = uint32_t(__float_as_int(q1.w));
+				ip = ray.origin + t * ray.direction;
+				if (dot3(ray.direction, nn) > 0) nn = -nn;
+			}
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth);
+			if (!alive) {
+				// the sample is complete: history.cl for this pixel, then its next sample (if any)
+				f4 h = ld4(w.hist[pixel]);
+				int32_t cnt = w.counts[pixel];
+				f4 cfold = color;
+				if (history_one(cfold, h, cnt, max_attempt)) {
+					w.sums[pixel] += color.x; w.sums[n + pixel] += color.y; w.sums[2 * n + pixel] += color.z;
+					w.sums[3 * n + pixel] += double(color.x) * color.x; w.sums[4 * n + pixel] += double(color.y) * color.y;
+					w.sums[5 * n + pixel] += double(color.z) * color.z;
+					w.sums[6 * n + pixel] += 1.0;
+				}
+				w.hist[pixel] = st4(h);
+				w.counts[pixel] = cnt;
+				w.seeds[pixel] = seed;
+				const int32_t left = frames_left[pixel] - 1;
+				frames_left[pixel] = left;
+				if (left > 0) {
+					ray = generate_ray(cam, uint32_t(pixel) % cam.width, uint32_t(pixel) / cam.width);
+					color = f4{1.0f, 1.0f, 1.0f, 0.0f};
+					alive = true;
+				}
+			}
+		}
+		const unsigned mask = __ballot_sync(0xffffffffu, alive);
+		if (mask) {
+			uint32_t qb = 0;
+			if (lane == 0) qb = atomicAdd(&w.qcount[round + 1], uint32_t(__popc(mask)));
+			qb = __shfl_sync(0xffffffffu, qb, 0);
+			if (alive) {
+				const uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+				__stcs(w.od[dst] + pos, st4(ray.origin));
+				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(pixel)));
+				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
+			}
+		}
+	}
+}
+
+__global__ void k_add_stats(unsigned long long* paths_done, unsigned long long paths, uint32_t* first_sample, uint32_t frames) {
+	*paths_done += paths;
+	*first_sample += frames;
+}
+
+__global__ void k_fill_i32(int32_t* p, int n, int32_t v) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) p[i] = v;
+}
+
 // ---- multi-GPU merge: acc[i] += peer_0[i] + peer_1[i] + ... with the peers' accumulators read in place over
 // NVLink peer mappings (mcpt_merge_sums).  Streaming, 8 B per element and peer; peers are added in index order.
 constexpr int MERGE_MAX_PEERS = 15;

@@ -9,6 +9,7 @@ from tests.util import adversarial_rays, hit_mismatches, hits_equal, random_rays
 
 pytestmark = pytest.mark.gpu
 
+REGEN_IS_DEFAULT = False      # mirrors MCPT_REGEN_DEFAULT of the library build
 ALL_TRAVERSALS = [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST, device.TRAVERSAL_CANONICAL, device.TRAVERSAL_WIDE8]
 SCENE_RES = {"cbox": (256, 256), "mis": (320, 180)}
 
@@ -217,6 +218,46 @@ def test_render_bit_exact(name, seed_mode, sif, request):
     np.testing.assert_allclose(sums[:3].T, ref["sum"], rtol=1e-12, atol=0)
     np.testing.assert_allclose(sums[3:6].T, ref["sumsq"], rtol=1e-12, atol=0)
     assert np.array_equal(sums[6], ref["counts"].astype(np.float64))
+
+
+@pytest.mark.parametrize("name", ["cbox", "mis"])
+def test_regenerated_paths_equal_the_frame_loop(name, request):
+    """seed_mode 0 renders of two or more samples regenerate paths (a finished pixel starts its next sample in the same
+    launch); the result must be the frame loop's: against the oracle, across two calls (seeds, history and counts carry
+    over), against single-sample calls (which take the frame path), and against the reference's own kernels."""
+    sc = request.getfixturevalue(name)
+    w, h = (96, 96) if name == "cbox" else (128, 72)
+    depth, cap = (8, 4) if name == "cbox" else (16, 9)
+    ref = O.render(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, depth, cap, 9, seed_mode=0, run_seed=5)
+    kw = dict(max_depth=depth, max_attempt=cap, seed_mode=0, run_seed=5)
+    import os
+    old = os.environ.get("MCPT_OPT")
+    os.environ["MCPT_OPT"] = str(int(old or 0) | (0 if REGEN_IS_DEFAULT else 16))    # read by mcpt_create
+    try:
+        a = _ctx(sc, w, h, **kw)
+    finally:
+        if old is None:
+            del os.environ["MCPT_OPT"]
+        else:
+            os.environ["MCPT_OPT"] = old
+    with a, _ctx(sc, w, h, **kw) as b:
+        a.render(5)
+        a.render(4)
+        for _ in range(9):
+            b.render(1)
+        for ctx in (a, b):
+            hist, counts = ctx.read_history()
+            assert hist.tobytes() == ref["hist"].tobytes() and np.array_equal(counts, ref["counts"])
+            st = ctx.stats()
+            assert st["rays_traced"] == ref["rays_traced"] and st["paths"] == 9 * w * h
+        assert a.read_sums().tobytes() == b.read_sums().tobytes()
+        assert np.array_equal(a.read_seeds(), b.read_seeds())
+    if O.refcl() is not None:
+        n = w * h
+        seeds = O.init_seeds(n, 5)
+        k_hist, k_cnt = np.zeros((n, 4), np.float32), np.zeros(n, np.int32)
+        O.refcl_update(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, depth, cap, 9, seeds, k_hist, k_cnt)
+        assert hist.tobytes() == k_hist.tobytes() and np.array_equal(counts, k_cnt)
 
 
 def test_frame_equals_render(cbox):
