@@ -292,7 +292,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 // is the longest chain of path lengths of any pixel), so rounds are enqueued in chunks and the live count is read
 // back after each chunk; rounds past the end find an empty queue and return at once.
 #ifndef MCPT_REGEN_DEFAULT
-#define MCPT_REGEN_DEFAULT 0
+#define MCPT_REGEN_DEFAULT 1
 #endif
 constexpr int REGEN_CHUNK = 1024;      // even: the queue parity carries over from chunk to chunk
 

@@ -9,7 +9,7 @@ from tests.util import adversarial_rays, hit_mismatches, hits_equal, random_rays
 
 pytestmark = pytest.mark.gpu
 
-REGEN_IS_DEFAULT = False      # mirrors MCPT_REGEN_DEFAULT of the library build
+REGEN_IS_DEFAULT = True       # mirrors MCPT_REGEN_DEFAULT of the library build
 ALL_TRAVERSALS = [device.TRAVERSAL_REFERENCE, device.TRAVERSAL_FAST, device.TRAVERSAL_CANONICAL, device.TRAVERSAL_WIDE8]
 SCENE_RES = {"cbox": (256, 256), "mis": (320, 180)}
 
