@@ -65,6 +65,8 @@ struct DevBuf {
 struct mcpt_ctx {
 	mcpt_params prm{};
 	cudaStream_t stream = nullptr;
+	cudaStream_t stream_g[4] = {nullptr, nullptr, nullptr, nullptr};   // streams of the regeneration loop's other pixel groups
+	cudaEvent_t ev_fork = nullptr;
 	int npix = 0;
 	bool have_scene = false, have_camera = false;
 	bool force_reference = false;     // node array violates box containment: monotonicity argument void
@@ -133,6 +135,8 @@ struct mcpt_ctx {
 
 	~mcpt_ctx() {
 		for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+		if (ev_fork) cudaEventDestroy(ev_fork);
+		for (cudaStream_t g : stream_g) if (g) cudaStreamDestroy(g);
 		if (stream) cudaStreamDestroy(stream);
 	}
 	// fold recorded event pairs into bounce_ms (requires the stream to be idle)
@@ -294,48 +298,85 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 #ifndef MCPT_REGEN_DEFAULT
 #define MCPT_REGEN_DEFAULT 1
 #endif
-constexpr int REGEN_CHUNK = 1024;      // even: the queue parity carries over from chunk to chunk
+constexpr int REGEN_CHUNK = 1024;
+constexpr int REGEN_MAX_GROUPS = 4;
+#ifndef MCPT_REGEN_GROUPS
+#define MCPT_REGEN_GROUPS 2
+#endif
+constexpr int REGEN_GROUPS = MCPT_REGEN_GROUPS;      // even: the queue parity carries over from chunk to chunk
 
 int enqueue_regen(mcpt_ctx* c, int frames) {
 	const int D = c->prm.max_depth;
 	const int n = c->npix;
 	if (int r = ensure_wave(c, 1)) return r;
-	CU(c->rq_count.alloc(REGEN_CHUNK + 2));
-	CU(c->rq_head.alloc(REGEN_CHUNK + 2));
+	// Several pixel groups, each on its own stream: a round's launches are small (one ray per unfinished pixel), and a persistent
+	// kernel's tail - its last warps finishing alone - is a third of such a launch; the other group's kernels fill it.
+	int G = (n >= (1 << 18) && !(c->opt_flags & 32)) ? REGEN_GROUPS : 1;
+	if (const char* e = std::getenv("MCPT_REGEN_GROUPS")) G = std::max(1, std::min(REGEN_MAX_GROUPS, std::atoi(e)));   // development
+	if (G > n) G = 1;
+	for (int k = 1; k < G; ++k)
+		if (!c->stream_g[k]) CU(cudaStreamCreateWithFlags(&c->stream_g[k], cudaStreamNonBlocking));
+	if (G > 1 && !c->ev_fork) CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+	const int RING = REGEN_CHUNK + 2;
+	CU(c->rq_count.alloc(size_t(REGEN_MAX_GROUPS) * RING));
+	CU(c->rq_head.alloc(size_t(REGEN_MAX_GROUPS) * RING));
 	CU(c->frames_left.alloc(size_t(n)));
-	WaveDev w = c->wave();
-	w.qcount = c->rq_count.p;
 	const int BS = c->block;
-	const int g = blocks(n, BS);
 	k_fill_i32<<<blocks(n, 256), 256, 0, c->stream>>>(c->frames_left.p, n, frames);
-	CU(cudaMemsetAsync(c->rq_count.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
-	CU(cudaMemsetAsync(c->rq_head.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
-	k_wave_generate<<<blocks(n, 256), 256, 0, c->stream>>>(c->cam, w, 1, 0, c->prm.run_seed);      // sample 1 of every pixel -> queue 0
-	c->launches += 2;
+	CU(cudaMemsetAsync(c->rq_count.p, 0, sizeof(uint32_t) * REGEN_MAX_GROUPS * RING, c->stream));
+	CU(cudaMemsetAsync(c->rq_head.p, 0, sizeof(uint32_t) * REGEN_MAX_GROUPS * RING, c->stream));
+	++c->launches;
+	struct Group { WaveDev w; uint32_t* head; cudaStream_t st; int count; uint32_t live; } grp[REGEN_MAX_GROUPS];
+	if (G > 1) CU(cudaEventRecord(c->ev_fork, c->stream));
+	for (int k = 0; k < G; ++k) {
+		const int p0 = int(long(n) * k / G);
+		const int cnt = int(long(n) * (k + 1) / G) - p0;
+		WaveDev w = c->wave();
+		for (int b2 = 0; b2 < 2; ++b2) { w.od[b2] += p0; w.dp[b2] += p0; w.cs[b2] += p0; }
+		w.hitrec += p0;
+		w.qcount = c->rq_count.p + size_t(k) * RING;
+		grp[k] = Group{w, c->rq_head.p + size_t(k) * RING, k == 0 ? c->stream : c->stream_g[k], cnt, uint32_t(cnt)};
+		if (k > 0) CU(cudaStreamWaitEvent(grp[k].st, c->ev_fork, 0));      // the other streams start after the set-up above
+		k_regen_start<<<blocks(cnt, 256), 256, 0, grp[k].st>>>(c->cam, w, p0, cnt);
+		++c->launches;
+	}
 	const long max_rounds = long(frames) * D;        // every path ends within D rounds of its start
 	long done_rounds = 0;
-	uint32_t live = uint32_t(n);
-	while (live > 0 && done_rounds < max_rounds) {
-		// a chunk no longer than what the live paths can still need at most, rounded up to an even count
-		long want = std::min<long>(REGEN_CHUNK, max_rounds - done_rounds);
-		const int rounds = int((want + 1) & ~1L);
+	bool any = true;
+	while (any && done_rounds < max_rounds) {
+		const long want = std::min<long>(REGEN_CHUNK, max_rounds - done_rounds);
+		const int rounds = int((want + 1) & ~1L);        // even: the queue parity carries over to the next chunk
 		for (int r = 0; r < rounds; ++r) {
-			k_wave_trace_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, r, c->prm.tmin, c->rq_head.p + r);
-			k_wave_shade_regen<<<std::min(blocks(n, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, c->cam, r, D, c->prm.max_attempt, c->frames_left.p);
+			for (int k = 0; k < G; ++k) {
+				if (!grp[k].live) continue;
+				k_wave_trace_persistent<<<std::min(blocks(grp[k].count, BS), c->persistent_grid(BS)), BS, 0, grp[k].st>>>(
+					c->scene, grp[k].w, r, c->prm.tmin, grp[k].head + r);
+			}
+			for (int k = 0; k < G; ++k) {
+				if (!grp[k].live) continue;
+				k_wave_shade_regen<<<std::min(blocks(grp[k].count, 256), c->nsm * 8), 256, 0, grp[k].st>>>(
+					c->scene, grp[k].w, c->cam, r, D, c->prm.max_attempt, c->frames_left.p);
+				c->launches += 2;
+			}
 		}
-		c->launches += 2 * uint64_t(rounds);
-		CU(cudaMemcpyAsync(&live, c->rq_count.p + rounds, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-		// carry the queue over: round `rounds` of this chunk is round 0 of the next (same parity, rounds is even)
-		CU(cudaMemcpyAsync(c->rq_count.p, c->rq_count.p + rounds, sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
-		CU(cudaMemsetAsync(c->rq_count.p + 1, 0, sizeof(uint32_t) * (REGEN_CHUNK + 1), c->stream));
-		CU(cudaMemsetAsync(c->rq_head.p, 0, sizeof(uint32_t) * (REGEN_CHUNK + 2), c->stream));
-		CU(cudaStreamSynchronize(c->stream));
+		for (int k = 0; k < G; ++k) {
+			if (!grp[k].live) continue;
+			uint32_t* q = grp[k].w.qcount;
+			CU(cudaMemcpyAsync(&grp[k].live, q + rounds, sizeof(uint32_t), cudaMemcpyDeviceToHost, grp[k].st));
+			// carry the queue over: round `rounds` of this chunk is round 0 of the next
+			CU(cudaMemcpyAsync(q, q + rounds, sizeof(uint32_t), cudaMemcpyDeviceToDevice, grp[k].st));
+			CU(cudaMemsetAsync(q + 1, 0, sizeof(uint32_t) * (RING - 1), grp[k].st));
+			CU(cudaMemsetAsync(grp[k].head, 0, sizeof(uint32_t) * RING, grp[k].st));
+		}
+		for (int k = 0; k < G; ++k) CU(cudaStreamSynchronize(grp[k].st));
 		done_rounds += rounds;
+		any = false;
+		for (int k = 0; k < G; ++k) any = any || grp[k].live != 0;
 	}
-	if (live != 0) return fail(MCPT_ERR_STATE, "mcpt_render: regeneration loop did not drain (internal error)");
+	if (any) return fail(MCPT_ERR_STATE, "mcpt_render: regeneration loop did not drain (internal error)");
 	// bookkeeping the frame loop does in k_wave_resolve
 	const unsigned long long paths = (unsigned long long)frames * (unsigned long long)n;
-	k_add_stats<<<1, 1, 0, c->stream>>>(w.paths_done, paths, w.first_sample, uint32_t(frames));
+	k_add_stats<<<1, 1, 0, c->stream>>>(grp[0].w.paths_done, paths, grp[0].w.first_sample, uint32_t(frames));
 	++c->launches;
 	CU(cudaGetLastError());
 	return MCPT_OK;

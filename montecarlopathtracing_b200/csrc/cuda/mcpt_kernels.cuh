@@ -605,7 +605,7 @@ __global__ void __launch_bounds__(256) k_wave_shade_regen(SceneDev sc, WaveDev w
 	const uint32_t total = w.qcount[round];
 	const unsigned lane = threadIdx.x & 31u;
 	const uint32_t stride = gridDim.x * blockDim.x;
-	if (blockIdx.x == 0 && threadIdx.x == 0) *w.rays_traced += total;
+	if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(w.rays_traced, (unsigned long long)total);   // pixel groups run concurrently
 	const size_t n = size_t(w.npix);
 	for (uint32_t bbase = blockIdx.x * blockDim.x; bbase < total; bbase += stride) {   // block-uniform trip count
 		const uint32_t i = bbase + threadIdx.x;
@@ -671,6 +671,18 @@ __global__ void __launch_bounds__(256) k_wave_shade_regen(SceneDev sc, WaveDev w
 			}
 		}
 	}
+}
+
+// first sample of pixels [p0, p0 + count): queue position j holds pixel p0 + j
+__global__ void __launch_bounds__(256) k_regen_start(CameraDev cam, WaveDev w, int p0, int count) {
+	const int j = blockIdx.x * blockDim.x + threadIdx.x;
+	if (j == 0) w.qcount[0] = uint32_t(count);
+	if (j >= count) return;
+	const int p = p0 + j;
+	RayRegs r = generate_ray(cam, uint32_t(p) % cam.width, uint32_t(p) / cam.width);
+	w.od[0][j] = st4(r.origin);
+	w.dp[0][j] = make_float4(r.direction.x, r.direction.y, r.direction.z, __int_as_float(p));
+	w.cs[0][j] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(int(w.seeds[p])));
 }
 
 __global__ void k_add_stats(unsigned long long* paths_done, unsigned long long paths, uint32_t* first_sample, uint32_t frames) {

@@ -260,6 +260,23 @@ def test_regenerated_paths_equal_the_frame_loop(name, request):
         assert hist.tobytes() == k_hist.tobytes() and np.array_equal(counts, k_cnt)
 
 
+def test_regeneration_with_two_pixel_groups(cbox):
+    """From 2^18 pixels on, the regeneration loop runs two pixel groups on two streams: same image as the oracle."""
+    w = h = 520
+    ref = O.render(cbox.camera, w, h, cbox.nodes, cbox.triangles, cbox.materials, 8, 3, 4, seed_mode=0, run_seed=2)
+    with _ctx(cbox, w, h, max_depth=8, max_attempt=3, seed_mode=0, run_seed=2) as ctx:
+        ctx.render(4)
+        hist, counts = ctx.read_history()
+        st = ctx.stats()
+        seeds = ctx.read_seeds()
+    assert hist.tobytes() == ref["hist"].tobytes() and np.array_equal(counts, ref["counts"])
+    assert st["rays_traced"] == ref["rays_traced"] and st["paths"] == 4 * w * h
+    with _ctx(cbox, w, h, max_depth=8, max_attempt=3, seed_mode=0, run_seed=2) as ctx:
+        for _ in range(4):
+            ctx.render(1)                       # frame path
+        assert np.array_equal(ctx.read_seeds(), seeds)
+
+
 def test_frame_equals_render(cbox):
     """The stage-kernel frame loop and the fused wavefront give the same image for the same seeds."""
     w = h = 64
