@@ -30,6 +30,7 @@
 #include <cfloat>
 #include <cstdint>
 #include <string>
+#include <vector>
 
 #include "mcpt.h"
 
@@ -91,14 +92,15 @@ __global__ void k_sah_first_leaf(const mcpt_bvh_node* __restrict__ nodes, int nl
 	const int4 lk0 = ld_link(nodes, first);
 	const int t = lk0.y;
 	bool bad = (t < 0 || t >= 2 * nleaves - 1 || t == first);
-	for (int a = lk0.x; a >= 0 && !bad; a = ld_link(nodes, a).x) bad = (a == t);
-	if (bad) { *status = 1; return; }
+	int steps = 0;                           // a parent chain longer than the node count is a cycle: malformed input
+	for (int a = lk0.x; a >= 0 && !bad; a = ld_link(nodes, a).x) bad = (a == t) || (++steps > 2 * nleaves);
+	if (bad) { *status = steps > 2 * nleaves ? 3 : 1; return; }
 	{
 		const float4 lo = ld_lo(nodes, first), hi = ld_hi(nodes, first);
 		const float st = __ldcg(sah + t);
 		sah[first] = st + st + C_INNER * area3(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z) / root_area;
 	}
-	for (int p = lk0.x; p >= 0;) {          // every sibling subtree on this chain is complete
+	for (int p = lk0.x; p >= 0;) {          // every sibling subtree on this chain is complete (chain length checked above)
 		const int4 lk = ld_link(nodes, p);
 		const float4 lo = ld_lo(nodes, p), hi = ld_hi(nodes, p);
 		const float sl = __ldcg(sah + lk.y), sr = __ldcg(sah + lk.z);
@@ -370,8 +372,32 @@ extern "C" int mcpt_optimize_treelet(int device, const mcpt_bvh_node* nodes_in, 
 		if (nodes_out != nodes_in) nodes_out[0] = nodes_in[0];
 		return nnodes;
 	}
-	TRY_(cudaSetDevice(device));
 	const int nleaves = (nnodes + 1) / 2;
+	// The kernels climb parent links and descend child links without bounds: make sure the array is ONE binary tree
+	// in the reference's layout (inner nodes 0..N-2, leaves N-1..2N-2, consistent parent links) before launching.
+	{
+		std::vector<int> todo{0};
+		std::vector<char> seen(size_t(nnodes), 0);
+		size_t reached = 0;
+		bool ok = nodes_in[0].parent == -1;
+		while (ok && !todo.empty()) {
+			const int i = todo.back();
+			todo.pop_back();
+			if (seen[size_t(i)]) { ok = false; break; }
+			seen[size_t(i)] = 1;
+			++reached;
+			const mcpt_bvh_node& nd = nodes_in[i];
+			if (i >= nleaves - 1) { ok = nd.left == nd.right; continue; }
+			ok = nd.left >= 0 && nd.left < nnodes && nd.right >= 0 && nd.right < nnodes && nd.left != nd.right &&
+			     nodes_in[nd.left].parent == i && nodes_in[nd.right].parent == i;
+			if (ok) { todo.push_back(nd.right); todo.push_back(nd.left); }
+		}
+		if (!ok || reached != size_t(nnodes)) {
+			set_last_error("mcpt_optimize_treelet: the node array is not a binary tree in the reference's layout (inner nodes first, consistent parent / child links)");
+			return MCPT_ERR_ARG;
+		}
+	}
+	TRY_(cudaSetDevice(device));
 	cudaStream_t st;
 	TRY_(cudaStreamCreate(&st));
 	struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } guard{st};
@@ -396,6 +422,10 @@ extern "C" int mcpt_optimize_treelet(int device, const mcpt_bvh_node* nodes_in, 
 	int h_status = 0;
 	TRY_(cudaMemcpyAsync(&h_status, status.p, sizeof(int), cudaMemcpyDeviceToHost, st));
 	TRY_(cudaStreamSynchronize(st));
+	if (h_status == 3) {
+		set_last_error("mcpt_optimize_treelet: the parent links of the first leaf do not reach the root (malformed node array)");
+		return MCPT_ERR_ARG;
+	}
 	if (h_status == 1) {                                 // same condition and wording as csrc/host/treelet.cpp
 		set_last_error("treelet: SAH recursion does not terminate for this node array");
 		return MCPT_ERR_STATE;

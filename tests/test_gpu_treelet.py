@@ -81,3 +81,12 @@ def test_first_leaf_triangle_id_decides_termination():
 def test_errors():
     with pytest.raises(device.McptError):
         device.optimize_treelet(np.zeros(4, T.BVH_NODE))
+    nodes = host.build_bvh(_random_tris(200, 3))
+    bad = nodes.copy()
+    bad[5]["parent"] = 7                              # inconsistent parent link: rejected before any kernel runs
+    with pytest.raises(device.McptError, match="binary tree"):
+        device.optimize_treelet(bad)
+    cyc = nodes.copy()
+    cyc[3]["left"] = 0                                # child link back to the root
+    with pytest.raises(device.McptError, match="binary tree"):
+        device.optimize_treelet(cyc)
