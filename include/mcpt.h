@@ -110,10 +110,7 @@ int mcpt_frame(mcpt_ctx* ctx);                              /* OpenCL::update():
 
 /* ---- fused wavefront path (the product): spp more samples for every pixel, all on the device ---- */
 int mcpt_render(mcpt_ctx* ctx, int spp);
-int mcpt_render_async(mcpt_ctx* ctx, int spp);              /* enqueue only; mcpt_synchronize to wait.  Exception: seed_mode 0
-                                                             * with spp >= 2 regenerates paths (a pixel's next sample starts
-                                                             * when its previous one ends) and waits for the live count
-                                                             * between chunks of rounds, so it returns with the work done */
+int mcpt_render_async(mcpt_ctx* ctx, int spp);              /* enqueue only; mcpt_synchronize to wait */
 int mcpt_set_first_sample(mcpt_ctx* ctx, uint32_t first);   /* seed_mode 1: global index of the next sample */
 int mcpt_reset_accumulation(mcpt_ctx* ctx);                 /* hist, count, sums <- 0; seeds re-derived */
 

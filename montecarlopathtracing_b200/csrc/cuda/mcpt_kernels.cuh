@@ -695,6 +695,123 @@ __global__ void k_fill_i32(int32_t* p, int n, int32_t v) {
 	if (i < n) p[i] = v;
 }
 
+// ---- seed_mode 0 without launch boundaries: one work item = one PIXEL, all `frames` samples of it.  A lane keeps its
+// pixel from ray to ray - walk, shade, then either the bounce ray or, when the path ended, the fold into hist /
+// counts / sums (history.cl, the pixel's own sample order) and the next sample's primary ray - and only fetches
+// another pixel when this one has no samples left.  No queues, no per-bounce launches, so none of the ~100 us a launch
+// waits for its last warp batch; the price is the shader running inside the walk kernel's refill phase
+// at partial lane occupancy.  Bit-identical to the frame loop: every pixel sees the same sequence of operations.
+template <class Job>
+__device__ __forceinline__ void persistent_walk_chain(const SceneDev& sc, float tmin, unsigned total, unsigned* head, Job& job) {
+	const unsigned FULL = 0xffffffffu;
+	const unsigned lane = threadIdx.x & 31u;
+	const unsigned lt_mask = (1u << lane) - 1u;
+	Walk2 w;
+	RayRegs ray;
+	bool working = false, have_result = false, exhausted = false;
+	for (;;) {
+		unsigned wm = __ballot_sync(FULL, working);
+		if (__popc(wm) < MCPT_REFILL_THRESHOLD) {
+			if (have_result) {
+				HitRegs h;
+				walk2_resolve<false>(w, sc, ray, tmin, h, nullptr, nullptr);
+				have_result = false;
+				if (job.next(ray, h)) {                        // the pixel goes on with `ray`
+					walk2_init(w, sc, ray);
+					working = true;
+				}
+			}
+			if (!exhausted) {
+				bool want = !working;
+				unsigned m = __ballot_sync(FULL, want);
+				while (m) {                                    // warp-uniform loop
+					const unsigned n = unsigned(__popc(m));
+					unsigned base = 0;
+					if (lane == unsigned(__ffs(int(m))) - 1u) base = atomicAdd(head, n);
+					base = __shfl_sync(FULL, base, __ffs(int(m)) - 1);
+					if (want) {
+						const unsigned i = base + unsigned(__popc(m & lt_mask));
+						if (i < total) {
+							job.start(i, ray);
+							walk2_init(w, sc, ray);
+							working = true;
+						}
+						want = false;
+					}
+					if (base + n >= total) exhausted = true;   // base, n are warp-uniform
+					m = 0u;
+				}
+			}
+			wm = __ballot_sync(FULL, working);
+			if (wm == 0u) break;
+		}
+		if (working) {
+			walk2_round<false>(w, sc, ray, tmin);
+			if (walk2_finished(w)) { working = false; have_result = true; }
+		}
+	}
+}
+
+struct PixelChainJob {
+	const SceneDev& sc;
+	const WaveDev& w;
+	const CameraDev& cam;
+	int frames, max_depth, max_attempt;
+	f4 color;
+	uint32_t seed;
+	int pixel, left;
+	unsigned long long traced;
+	__device__ __forceinline__ void start(unsigned i, RayRegs& ray) {
+		pixel = int(i);
+		left = frames;
+		traced = 0;
+		seed = w.seeds[pixel];
+		color = f4{1.0f, 1.0f, 1.0f, 0.0f};
+		ray = generate_ray(cam, uint32_t(pixel) % cam.width, uint32_t(pixel) / cam.width);
+	}
+	__device__ __forceinline__ bool next(RayRegs& ray, const HitRegs& h) {
+		++traced;
+		f4 nn{0, 0, 0, 0}, ip{0, 0, 0, 0};
+		uint32_t mat = 0;
+		if (h.closest >= 0) {
+			const float4* tp = reinterpret_cast<const float4*>(sc.leaves + h.closest);
+			float4 q1 = __ldg(tp + 1), q2 = __ldg(tp + 2), q3 = __ldg(tp + 3), q4 = __ldg(tp + 4);
+			nn = f4{q2.w, q3.w, q4.w, 0.0f};
+			mat = uint32_t(__float_as_int(q1.w));
+			ip = ray.origin + h.t * ray.direction;
+			if (dot3(ray.direction, nn) > 0) nn = -nn;
+		}
+		if (shade_one(sc.materials, sc.cs_table, ray, h.t, nn, ip, mat, color, seed, max_depth)) return true;
+		// the sample is complete: history.cl for this pixel
+		const size_t n = size_t(w.npix);
+		f4 hs = ld4(w.hist[pixel]);
+		int32_t cnt = w.counts[pixel];
+		f4 cfold = color;
+		if (history_one(cfold, hs, cnt, max_attempt)) {
+			w.sums[pixel] += color.x; w.sums[n + pixel] += color.y; w.sums[2 * n + pixel] += color.z;
+			w.sums[3 * n + pixel] += double(color.x) * color.x; w.sums[4 * n + pixel] += double(color.y) * color.y;
+			w.sums[5 * n + pixel] += double(color.z) * color.z;
+			w.sums[6 * n + pixel] += 1.0;
+		}
+		w.hist[pixel] = st4(hs);
+		w.counts[pixel] = cnt;
+		if (--left == 0) {
+			w.seeds[pixel] = seed;
+			atomicAdd(w.rays_traced, traced);
+			return false;
+		}
+		ray = generate_ray(cam, uint32_t(pixel) % cam.width, uint32_t(pixel) / cam.width);
+		color = f4{1.0f, 1.0f, 1.0f, 0.0f};
+		return true;
+	}
+};
+
+__global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_pixel_chain(SceneDev sc, WaveDev w, CameraDev cam, int frames, int max_depth,
+                                                                        int max_attempt, float tmin, unsigned* head) {
+	PixelChainJob job{sc, w, cam, frames, max_depth, max_attempt, f4{0, 0, 0, 0}, 0u, 0, 0, 0ull};
+	persistent_walk_chain(sc, tmin, unsigned(w.npix), head, job);
+}
+
 // ---- multi-GPU merge: acc[i] += peer_0[i] + peer_1[i] + ... with the peers' accumulators read in place over
 // NVLink peer mappings (mcpt_merge_sums).  Streaming, 8 B per element and peer; peers are added in index order.
 constexpr int MERGE_MAX_PEERS = 15;

@@ -260,11 +260,23 @@ def test_regenerated_paths_equal_the_frame_loop(name, request):
         assert hist.tobytes() == k_hist.tobytes() and np.array_equal(counts, k_cnt)
 
 
-def test_regeneration_with_two_pixel_groups(cbox):
-    """From 2^18 pixels on, the regeneration loop runs two pixel groups on two streams: same image as the oracle."""
+@pytest.mark.parametrize("opt", [0, 64])
+def test_regeneration_at_a_quarter_megapixel(cbox, opt):
+    """opt 0: the pixel-chain kernel (default); opt 64: the queue-based loop, which from 2^18 pixels on runs two pixel
+    groups on two streams.  Same image as the oracle either way."""
+    import os
     w = h = 520
     ref = O.render(cbox.camera, w, h, cbox.nodes, cbox.triangles, cbox.materials, 8, 3, 4, seed_mode=0, run_seed=2)
-    with _ctx(cbox, w, h, max_depth=8, max_attempt=3, seed_mode=0, run_seed=2) as ctx:
+    old = os.environ.get("MCPT_OPT")
+    os.environ["MCPT_OPT"] = str(opt)                    # read by mcpt_create
+    try:
+        first = _ctx(cbox, w, h, max_depth=8, max_attempt=3, seed_mode=0, run_seed=2)
+    finally:
+        if old is None:
+            del os.environ["MCPT_OPT"]
+        else:
+            os.environ["MCPT_OPT"] = old
+    with first as ctx:
         ctx.render(4)
         hist, counts = ctx.read_history()
         st = ctx.stats()
