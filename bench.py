@@ -10,16 +10,27 @@ work is fixed, ranks own disjoint sample indices, scene + BVH replicated).
   value      Mrays/s, whole job, device-timed (CUDA events on the library's stream, max over ranks),
              scene resident in HBM.
   e2e        the same metric through the C ABI with HOST buffers: every step uploads the scene from
-             pinned host memory (mcpt_upload_scene + mcpt_set_camera), renders, and reads the merged
+             pinned host memory (mcpt_upload_scene_tagged + mcpt_set_camera), renders, and reads the merged
              sums back to the host (mcpt_read_sums); wall clock around the calls.
   roofline   the dominant kernel k_wave_trace_persistent (the BVH walk of one bounce): algorithmic bytes
              per ray (nodes, leaf boxes and triangles fetched, counted by an instrumented pass of the same
-             walk, + 40 B ray in / hit out) x rays / summed CUDA-event time of its launches, against the measured HBM copy
-             bandwidth (MEASURED_PEAKS.json).  The scene is L2-resident, so frac can exceed what HBM
-             traffic alone would allow; traffic (ncu dram bytes per launch) is read from profiles/.
-  cpu_baseline / --impl reference: the CPU oracle (a line-by-line port of the reference's OpenCL
-             kernels, which cannot be compiled here: no OpenCL platform, no clang) on all host cores,
-             on a bounded sample of the same workload (960x540, same camera/scene/depth).
+             walk, + 40 B ray in / hit out) x rays / summed CUDA-event time of its launches.  The scene is
+             L2/L1-resident (ncu: DRAM serves 3 % of those bytes), so the bound is "l2": peak = the L2
+             streaming-read ceiling (measured in this run by mcpt_measure_read_bandwidth and recorded, with the
+             probe's own ncu line, in profiles/l2_peak.json).  `hbm` carries the measured DRAM bytes against
+             MEASURED_PEAKS.json; `counters` the ncu figures of the same kernel at this configuration
+             (profiles/r2_walk_counters.json): lanes per instruction, issue-active, L1 pipe, stalls.
+  scenes     the metric names three scenes: short device-timed runs of cbox 1024x1024 depth 8 and veach_mis
+             1280x720 depth 16 (Mrays/s, Mpaths/s), N = 1 only.
+  reference_seeding   seed_mode 0 (the reference's one-LCG-stream-per-pixel, i.e. the drop-in update() semantics):
+             the same workload through k_pixel_chain, and frame by frame as OpenCL::update would call it.
+  strong_scaling      a fixed total of samples split over the ranks by sharding.sample_range, timed from the first
+             launch to the merged sums on rank 0 (max over ranks); init (context + upload) reported beside it.
+  cpu_baseline / --impl reference: the reference's OWN kernels (kernels/*.cl + objdef.h compiled as C++,
+             oracle/_ref/libmcpt_refcl.so; the oracle port only where that was never built) on all host
+             cores, on a bounded sample of the same workload (960x540 view, same camera/scene/depth).
+  parity_check        the image the cpu_baseline leg computed anyway, compared bit for bit with a GPU render of
+             the same seeds: every driver run re-proves parity on the timed scene.
 """
 import argparse
 import json
@@ -31,6 +42,7 @@ import time
 
 import numpy as np
 
+T_PROCESS_START = time.perf_counter()
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -50,6 +62,8 @@ def parse_args():
     ap.add_argument("--spp-per-step", type=int, default=16)
     ap.add_argument("--samples-in-flight", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the scenes / reference_seeding / strong_scaling sections (A/B runs)")
+    ap.add_argument("--strong-spp", type=int, default=4096, help="total samples of the strong-scaling section (BASELINE configs[4]: 4096)")
     ap.add_argument("--microbench-rays", type=int, default=1 << 24,
                     help="rays per set of the intersection microbench (BASELINE configs[1] uses 64 Mi; 0 = skip)")
     return ap.parse_args()
@@ -104,10 +118,28 @@ def cpu_sample(a, min_seconds=10.0, max_passes=8):
         paths += w * h
         passes += 1
     dt = time.perf_counter() - t0
+    image = {"w": w, "h": h, "spp": passes, "hist": hist, "counts": counts, "run_seed": 1, "rays": rays} if use_ref else None
     return {"value": rays / dt / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference" if use_ref else "port",
             "sample": "%dx%d, %d spp, depth %d, same scene and camera (%.1f s of CPU work)%s" %
                       (w, h, passes, a.depth, dt, ", the reference's kernels/*.cl compiled as C++ with OpenMP over work items" if use_ref else ""),
-            "mpaths_per_s": paths / dt / 1e6}, rays, paths, dt
+            "mpaths_per_s": paths / dt / 1e6}, rays, paths, dt, image
+
+
+def parity_check(a, image, local):
+    """The reference-kernel image of the cpu_baseline leg against mcpt_render (seed_mode 0, same run seed) on the GPU:
+    running mean, counts and ray count must agree bit for bit."""
+    from montecarlopathtracing_b200 import device, scenes
+    sc = scenes.load(a.scene)
+    w, h = image["w"], image["h"]
+    with device.Context(w, h, a.depth, 1 << 20, device=local, seed_mode=0, run_seed=image["run_seed"]) as g:
+        g.upload_scene(sc.triangles, sc.materials, sc.nodes)
+        g.set_camera(sc.camera)
+        g.render(image["spp"])
+        hist, counts = g.read_history()
+        traced = g.stats()["rays_traced"]
+    bad = (hist.view(np.uint32) != image["hist"].view(np.uint32)).any(axis=1) | (counts != image["counts"])
+    return {"against": "the reference's kernels (cpu_baseline leg), %dx%d x %d spp, depth %d, seed_mode 0" % (w, h, image["spp"], a.depth),
+            "pixels": int(w * h), "mismatches": int(bad.sum()), "rays_traced_equal": bool(traced == image["rays"])}
 
 
 def run_reference(a):
@@ -120,7 +152,7 @@ def run_reference(a):
     tot_rays = tot_dt = tot_paths = 0
     last = None
     for _ in range(a.steps):
-        last, rays, paths, dt = cpu_sample(a, min_seconds=0.0, max_passes=1)
+        last, rays, paths, dt, _ = cpu_sample(a, min_seconds=0.0, max_passes=1)
         tot_rays += rays
         tot_paths += paths
         tot_dt += dt
@@ -128,10 +160,16 @@ def run_reference(a):
     last.update(value=v, sample="%dx%d, 1 spp per step, depth %d, same scene and camera%s" %
                 (a.width // 2, a.height // 2, a.depth, ", the reference's kernels/*.cl compiled as C++ with OpenMP over work items" if last["kind"] == "reference" else ""),
                 mpaths_per_s=tot_paths / tot_dt / 1e6)
+    cfg = workload_config(a, a.gpus)
+    # what this arm actually runs per step: a rate-normalised slice of the workload (the metric is a rate)
+    cfg["reference_arm_slice"] = {"resolution": [a.width // 2, a.height // 2], "spp_per_step": 1, "max_depth": a.depth,
+                                  "note": "reduced slice of the same scene and camera, rate-normalised: Mrays/s does not "
+                                          "depend on the frame size, so the ratio against the GPU arm's full-size steps stands"}
+    cfg["workload"] += " [reference arm: %dx%d x 1 spp per step of it]" % (a.width // 2, a.height // 2)
     print(json.dumps({"impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": a.gpus,
                       "steps": a.steps, "warmup": a.warmup, "ms_per_step": tot_dt / a.steps * 1e3,
                       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                      "data": "synthetic", "config": workload_config(a, a.gpus), "cpu_baseline": last,
+                      "data": "synthetic", "config": cfg, "cpu_baseline": last,
                       "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                       "gpu_launches": 0}))
 
@@ -230,6 +268,60 @@ def microbench(ctx, sc, a, torch):
     return res
 
 
+
+def scene_section(name, w, h, depth, spp, reps, local, torch):
+    """Short device-timed run of another BASELINE scene (seed_mode 1, automatic wave size): Mrays/s and Mpaths/s."""
+    from montecarlopathtracing_b200 import device, scenes
+    sc = scenes.load(name)
+    with device.Context(w, h, depth, 1 << 30, device=local, seed_mode=1, run_seed=2024) as g:
+        g.upload_scene(sc.triangles, sc.materials, sc.nodes)
+        g.set_camera(sc.camera)
+        stream = torch.cuda.ExternalStream(g.stream)
+        g.render(spp)
+        g.reset_stats()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(reps):
+            g.render_async(spp)
+        e1.record(stream)
+        e1.synchronize()
+        ms = e0.elapsed_time(e1)
+        st = g.stats()
+    return {"workload": "Scene/%s %dx%d, max depth %d, %d x %d spp" % (name, w, h, depth, reps, spp),
+            "mrays_per_s": st["rays_traced"] / ms / 1e3, "mpaths_per_s": st["paths"] / ms / 1e3,
+            "rays_per_path": st["rays_traced"] / max(1, st["paths"]), "ms": ms, "gpu_launches": st["kernel_launches"]}
+
+
+def reference_seeding_section(a, sc, local, torch):
+    """seed_mode 0 = the reference's own seeding (one LCG stream per pixel, shade.cl:101): what a drop-in
+    OpenCL::update() runs.  `chain`: one mcpt_render(spp) call (k_pixel_chain); `frame_loop`: spp calls of
+    mcpt_render_async(1) + one synchronize, the way INTEGRATION.md's update() enqueues frames."""
+    from montecarlopathtracing_b200 import device
+    out = {}
+    spp = 8
+    with device.Context(a.width, a.height, a.depth, 1 << 30, device=local, seed_mode=0, run_seed=2024) as g:
+        g.upload_scene(sc.triangles, sc.materials, sc.nodes)
+        g.set_camera(sc.camera)
+        stream = torch.cuda.ExternalStream(g.stream)
+        for label in ("chain", "frame_loop"):
+            g.render(2)
+            g.reset_stats()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            if label == "chain":
+                g.render_async(spp)
+            else:
+                for _ in range(spp):
+                    g.render_async(1)
+            e1.record(stream)
+            e1.synchronize()
+            ms = e0.elapsed_time(e1)
+            st = g.stats()
+            out[label] = {"mrays_per_s": st["rays_traced"] / ms / 1e3, "mpaths_per_s": st["paths"] / ms / 1e3, "ms": ms,
+                          "spp": spp, "gpu_launches": st["kernel_launches"]}
+    out["workload"] = "Scene/%s %dx%d, max depth %d, seed_mode 0" % (a.scene, a.width, a.height, a.depth)
+    return out
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -253,9 +345,13 @@ def run_b200(a):
     npix = W * H
     sc = scenes.load(a.scene)
     total_steps = a.warmup + a.steps + 2
+    t_up = time.perf_counter()
     ctx = device.Context(W, H, D, 1 << 30, device=local, seed_mode=1, run_seed=2024, samples_in_flight=a.samples_in_flight)
-    ctx.upload_scene(sc.triangles, sc.materials, sc.nodes)
+    ctx.upload_scene(sc.triangles, sc.materials, sc.nodes)       # first upload of the process: derives the fast-walk layout
     ctx.set_camera(sc.camera)
+    ctx.synchronize()
+    cold_upload_s = time.perf_counter() - t_up
+    init_s = time.perf_counter() - T_PROCESS_START                # interpreter + torch + CUDA start-up + scene load + upload
     stream = torch.cuda.ExternalStream(ctx.stream)
     sums = torch.zeros(7 * npix, dtype=torch.float64, device="cuda")
     ctx.bind_sums(sums.data_ptr())
@@ -324,7 +420,7 @@ def run_b200(a):
     lib = device.lib()
 
     def e2e_step():
-        ctx.upload_scene(h_tris, h_mats, h_nodes)
+        ctx.upload_scene(h_tris, h_mats, h_nodes, geometry_tag=1)      # same geometry every step: generation counter 1
         ctx.set_camera(h_cam)
         ctx.render_async(SPP)
         merge()
@@ -351,17 +447,60 @@ def run_b200(a):
     h2d = sc.scene_bytes
     d2h = 7 * 8 * npix
 
+    # ---- strong scaling: a FIXED total of samples split over the ranks, timed to the merged sums (all ranks take part)
+    strong = None
+    if not a.no_extras and a.strong_spp > 0:
+        first, count = sharding.sample_range(rank, world, a.strong_spp)
+        ctx.reset_accumulation()
+        ctx.set_first_sample(first)
+        ctx.reset_stats()
+        fence()
+        t0 = time.perf_counter()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        ctx.render_async(count)
+        merge()
+        s1.record(stream)
+        if rank == 0:
+            ctx._call("mcpt_read_sums", device._vp(h_out))        # the image's sums on the host
+        else:
+            ctx.synchronize()
+        wall = time.perf_counter() - t0
+        s1.synchronize()
+        st3 = ctx.stats()
+        t3 = torch.tensor([s0.elapsed_time(s1) * 1e-3, wall, init_s, cold_upload_s], dtype=torch.float64, device="cuda")
+        c3 = torch.tensor([st3["rays_traced"], st3["paths"]], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+            dist.all_reduce(c3, op=dist.ReduceOp.SUM)
+        dev_s, wall_s, init_max, cold_max = t3.tolist()
+        strong = {"total_spp": a.strong_spp, "spp_per_gpu": count, "render_and_merge_s": dev_s,
+                  "time_to_image_s": wall_s, "init_s": init_max, "time_to_image_with_init_s": wall_s + init_max,
+                  "mrays_per_s": c3[0].item() / dev_s / 1e6, "mpaths_per_s": c3[1].item() / dev_s / 1e6,
+                  "how": "sample indices [first, first+count) per rank (sharding.sample_range), one reduce of the 7 sum planes onto "
+                         "rank 0 inside the timed region; render_and_merge_s = CUDA events, max over ranks; time_to_image_s = wall "
+                         "clock to the merged sums on rank 0's host; init_s = process start to scene resident (max over ranks)"}
+        fence()
+
     if rank == 0:
         peaks = read_json(os.path.join(ROOT, "MEASURED_PEAKS.json"))
-        peak = float(peaks["hbm_gbs"]) if peaks and "hbm_gbs" in peaks else 6650.0
+        hbm_peak = float(peaks["hbm_gbs"]) if peaks and "hbm_gbs" in peaks else 6650.0
         prof = read_json(os.path.join(ROOT, "profiles", "traffic.json")) or {}
+        counters = read_json(os.path.join(ROOT, "profiles", "r2_walk_counters.json"))
+        l2_rec = read_json(os.path.join(ROOT, "profiles", "l2_peak.json")) or {}
         achieved = bytes_per_ray * (rays / world) / (bounce_ms_max * 1e-3) / 1e9 if bounce_ms_max > 0 else None
-        # the walk's bytes come out of L1/L2, not HBM: measure the L2 streaming-read ceiling next to it (32 MiB buffer)
+        # The walk's bytes come out of L1/L2 (ncu: DRAM serves 3 % of them), so the ceiling it lives under is the L2
+        # streaming-read bandwidth: measured here (32 MiB buffer, ld.global.cg) and recorded in profiles/l2_peak.json
         try:
             l2_peak = device.measure_read_bandwidth(32 << 20, iters=40, device=local)
         except Exception as e:      # measurement aid only
-            l2_peak = None
+            l2_peak = l2_rec.get("l2_read_gbs")
             sys.stderr.write("l2 probe failed: %s\n" % e)
+        frac = (achieved / l2_peak) if (achieved and l2_peak) else None
+        if frac is not None and frac > 1.0:
+            sys.stderr.write("roofline: frac %.3f > 1 - the L2 ceiling is not what bounds this kernel\n" % frac)
+        dram = prof.get("dram_bytes_per_launch")
+        avg_launch_s = (bounce_ms_max / max(1, bounce_launches)) * 1e-3
         out = {
             "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -370,26 +509,47 @@ def run_b200(a):
             "time_to_4096_spp_s": 4096.0 / (world * SPP) * (ms_max / a.steps) * 1e-3,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "ms_per_step": t2.item() / a.steps * 1e3},
+            "cold_upload_s": cold_upload_s,
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k_wave_trace_persistent", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": (achieved / peak) if achieved else None,
-                         "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
-                         "traffic": prof.get("dram_bytes_per_launch"),
+            "roofline": {"bound": "l2", "kernel": "k_wave_trace_persistent", "achieved": achieved, "peak": l2_peak,
+                         "unit": "GB/s", "frac": frac,
+                         "peak_source": "L2 streaming-read ceiling measured in this run (mcpt_measure_read_bandwidth: ld.global.cg over a "
+                                        "32 MiB buffer, 148x8 blocks, best of 5); recorded with the probe's ncu line in profiles/l2_peak.json",
+                         "peak_recorded": l2_rec.get("l2_read_gbs"),
+                         "traffic": dram,
                          "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "leaves_per_ray": leaves_per_ray,
                          "tris_per_ray": tris_per_ray,
                          "kernel_ms_per_step": bounce_ms_max / a.steps, "kernel_launches": int(bounce_launches),
                          "kernel_share_of_step": bounce_ms_max / ms_max,
-                         "l2": {"peak": l2_peak, "unit": "GB/s", "frac": (achieved / l2_peak) if (achieved and l2_peak) else None,
-                                "how": "streaming ld.global.cg read of a 32 MiB buffer, 148x8 blocks, best of 5"},
-                         "note": "algorithmic bytes are served mostly by L1/L2 (scene is L2-resident): frac is against "
-                                 "what HBM could feed; l2.frac is the same bytes against the measured L2 read ceiling; "
-                                 "the binding unit per ncu is the L1 data pipe (profiles/r1h_trace_shade_ncu_full.txt)"},
+                         "hbm": {"peak": hbm_peak, "unit": "GB/s",
+                                 "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                                 "achieved_dram": (dram / avg_launch_s / 1e9) if (dram and avg_launch_s > 0) else None,
+                                 "frac_dram": (dram / avg_launch_s / 1e9 / hbm_peak) if (dram and avg_launch_s > 0) else None,
+                                 "algorithmic_over_hbm_peak": (achieved / hbm_peak) if achieved else None,
+                                 "note": "achieved_dram = ncu dram bytes per launch (profiles/traffic.json, captured at this configuration) / "
+                                         "the average launch time of this run: HBM is not the bound; algorithmic_over_hbm_peak > 1 only says "
+                                         "the walk's appetite exceeds what HBM alone could feed"},
+                         "counters": counters,
+                         "note": "bound l2: the algorithmic bytes are served by L1/L2 (scene L2-resident); what keeps the kernel below the "
+                                 "L2 ceiling is instruction issue under SIMT divergence plus dependent-load latency - see counters "
+                                 "(lanes per instruction, issue-active, long-scoreboard stalls) and DESIGN.md §5/§10"},
             "clocks": clk,
         }
+        if strong:
+            out["strong_scaling"] = strong
         if world == 1 and a.microbench_rays > 0:
             out["microbench"] = microbench(ctx, sc, a, torch)
+    if rank == 0 and world == 1 and not a.no_extras:
+        ctx.close()
+        out["scenes"] = {"cbox": scene_section("cbox", 1024, 1024, 8, 64, 2, local, torch),
+                         "veach_mis": scene_section("veach_mis", 1280, 720, 16, 64, 2, local, torch)}
+        out["reference_seeding"] = reference_seeding_section(a, sc, local, torch)
+    if rank == 0:
         if world == 1 and not a.no_cpu_baseline:
-            out["cpu_baseline"] = cpu_sample(a)[0]
+            base, _, _, _, image = cpu_sample(a)
+            out["cpu_baseline"] = base
+            if image is not None:
+                out["parity_check"] = parity_check(a, image, local)
         print(json.dumps(out))
     ctx.close()
     if world > 1:

@@ -97,6 +97,11 @@ int mcpt_synchronize(mcpt_ctx* ctx);
  * mcpt_host_build_bvh (reference layout); the device traversal layout is derived here. */
 int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes);
+/* Same, with the caller's generation counter for the geometry: a non-zero tag equal to the previous upload's tag tells
+ * the library that tris and nodes hold the same bytes as last time, so it re-copies the arrays (like the reference's
+ * CL_MEM_COPY_HOST_PTR buffers, oclbasic.h:56-58) without comparing 80 MB to find that out.  Tag 0 = no promise. */
+int mcpt_upload_scene_tagged(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                             const mcpt_bvh_node* nodes, int nnodes, uint64_t geometry_tag);
 int mcpt_set_camera(mcpt_ctx* ctx, const mcpt_camera* cam);
 
 /* ---- stage level: one call = one reference kernel over the W*H work items (reference buffer layouts) ---- */
@@ -111,7 +116,9 @@ int mcpt_frame(mcpt_ctx* ctx);                              /* OpenCL::update():
 /* ---- fused wavefront path (the product): spp more samples for every pixel, all on the device ---- */
 int mcpt_render(mcpt_ctx* ctx, int spp);
 int mcpt_render_async(mcpt_ctx* ctx, int spp);              /* enqueue only; mcpt_synchronize to wait */
-int mcpt_set_first_sample(mcpt_ctx* ctx, uint32_t first);   /* seed_mode 1: global index of the next sample */
+int mcpt_set_first_sample(mcpt_ctx* ctx, uint32_t first);   /* seed_mode 1: global index of the next sample (seed_mode 0:
+                                                               MCPT_ERR_STATE unless first == 0 - it cannot shard) */
+int mcpt_get_first_sample(mcpt_ctx* ctx, uint32_t* first);  /* samples rendered so far + the first index set */
 int mcpt_reset_accumulation(mcpt_ctx* ctx);                 /* hist, count, sums <- 0; seeds re-derived */
 
 /* ---- buffer I/O (blocking, like readBuffer/writeBuffer with CL_TRUE) ---- */
@@ -126,6 +133,11 @@ int mcpt_write_seeds(mcpt_ctx* ctx, const uint32_t* src);
 int mcpt_read_history(mcpt_ctx* ctx, float* hist_rgba, int32_t* counts /* may be NULL */);
 /* 7 planes of W*H doubles: sum r,g,b; sum of squares r,g,b; counted (non-zero, capped) samples */
 int mcpt_read_sums(mcpt_ctx* ctx, double* dst);
+/* Checkpoint / resume (the reference keeps its progressive state device-resident and dumps once, colorout.cpp:23-24,
+ * 49-50, 63-68): what mcpt_read_history / mcpt_read_sums / mcpt_read_seeds / mcpt_get_first_sample returned can be put
+ * back into a fresh context of the same size, and rendering continues bit for bit where it stopped. */
+int mcpt_write_sums(mcpt_ctx* ctx, const double* src);
+int mcpt_write_history(mcpt_ctx* ctx, const float* hist_rgba, const int32_t* counts);
 /* Accumulate the sums in caller-owned DEVICE memory (7*W*H doubles, e.g. the NCCL reduce buffer); NULL = own. */
 int mcpt_bind_sums(mcpt_ctx* ctx, double* device_ptr);
 

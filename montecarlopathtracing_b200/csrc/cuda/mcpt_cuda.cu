@@ -124,6 +124,7 @@ struct mcpt_ctx {
 	int opt_flags = 0, block = 128;          // development switches: env MCPT_OPT, MCPT_BLOCK
 	std::vector<mcpt_triangle> cache_tris;   // host copy of the last upload (derived-layout cache key)
 	std::vector<mcpt_bvh_node> cache_nodes;
+	uint64_t geometry_tag = 0;               // caller's generation counter of the last upload (mcpt_upload_scene_tagged)
 	uint64_t launches = 0;
 	uint64_t stage_paths = 0;
 	// measurement aids
@@ -730,16 +731,33 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 	return MCPT_OK;
 }
 
+static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag);
+
 int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes) {
+	return upload_scene(c, tris, ntris, mats, nmats, nodes, nnodes, 0);
+}
+
+int mcpt_upload_scene_tagged(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                             const mcpt_bvh_node* nodes, int nnodes, uint64_t geometry_tag) {
+	return upload_scene(c, tris, ntris, mats, nmats, nodes, nnodes, geometry_tag);
+}
+
+static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag) {
 	if (int r = check_ctx(c, false, false)) return r;
 	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
 		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
 	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
 	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
+	// A non-zero geometry_tag equal to the previous upload's is the caller's word that triangles and nodes are the same
+	// bytes (a generation counter); without one the two arrays are compared (80 MB for the diningroom stand-in).
+	const bool same_tag = tag != 0 && tag == c->geometry_tag;
 	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
-	    bytes_equal(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
-	    bytes_equal(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)) {
+	    (same_tag || (bytes_equal(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
+	                  bytes_equal(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)))) {
+		c->geometry_tag = tag;
 		for (int m = 0; m < nmats; ++m)
 			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
 				return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
@@ -856,6 +874,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const m
 	}
 	c->cache_tris.assign(tris, tris + ntris);
 	c->cache_nodes.assign(nodes, nodes + nnodes);
+	c->geometry_tag = tag;
 	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs, have_q ? d_qnodes : nullptr, qframe};
 	c->have_scene = true;
 	return build_emitters(c, tris, ntris, mats);
@@ -992,6 +1011,10 @@ int mcpt_render(mcpt_ctx* c, int spp) {
 
 int mcpt_set_first_sample(mcpt_ctx* c, uint32_t first) {
 	if (int r = check_ctx(c, false, false)) return r;
+	// seed_mode 0 never reads the sample index (one LCG stream per pixel): ranks that "shard" it would all draw the
+	// same samples, silently.  Only the bookkeeping value 0 (a reset) is accepted there.
+	if (c->prm.seed_mode == 0 && first != 0)
+		return fail(MCPT_ERR_STATE, "mcpt_set_first_sample: seed_mode 0 has one stream per pixel and cannot be sharded by sample index (use seed_mode 1)");
 	CU(cudaMemcpyAsync(c->first_sample.p, &first, sizeof(first), cudaMemcpyHostToDevice, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	return MCPT_OK;
@@ -1045,6 +1068,34 @@ int mcpt_read_sums(mcpt_ctx* c, double* dst) {
 	if (int r = check_ctx(c, false, false)) return r;
 	if (!dst) return fail(MCPT_ERR_ARG, "mcpt_read_sums: null buffer");
 	CU(cudaMemcpyAsync(dst, c->sums, sizeof(double) * 7 * size_t(c->npix), cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+// ---- checkpoint / resume of the progressive state (the reference keeps hist / counts / seeds device-resident and
+// dumps once, colorout.cpp:23-24,49-50,63-68): together with mcpt_write_seeds (seed_mode 0) or
+// mcpt_set_first_sample (seed_mode 1) these restore a context to where mcpt_read_history / mcpt_read_sums left it.
+int mcpt_write_sums(mcpt_ctx* c, const double* src) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!src) return fail(MCPT_ERR_ARG, "mcpt_write_sums: null buffer");
+	CU(cudaMemcpyAsync(c->sums, src, sizeof(double) * 7 * size_t(c->npix), cudaMemcpyHostToDevice, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_write_history(mcpt_ctx* c, const float* hist_rgba, const int32_t* counts) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!hist_rgba || !counts) return fail(MCPT_ERR_ARG, "mcpt_write_history: null buffer");
+	CU(cudaMemcpyAsync(c->hist.p, hist_rgba, sizeof(float4) * c->npix, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaMemcpyAsync(c->counts.p, counts, sizeof(int32_t) * c->npix, cudaMemcpyHostToDevice, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_get_first_sample(mcpt_ctx* c, uint32_t* first) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!first) return fail(MCPT_ERR_ARG, "mcpt_get_first_sample: null output");
+	CU(cudaMemcpyAsync(first, c->first_sample.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
 	return MCPT_OK;
 }

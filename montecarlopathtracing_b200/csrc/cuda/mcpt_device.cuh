@@ -62,8 +62,12 @@ __device__ __forceinline__ f4 ld4(const mcpt_float4& v) { return {v.x, v.y, v.z,
 __device__ __forceinline__ f4 ld4(float4 v) { return {v.x, v.y, v.z, v.w}; }
 __device__ __forceinline__ float4 st4(f4 v) { return make_float4(v.x, v.y, v.z, v.w); }
 
-// Transcendentals: the correctly rounded float result, obtained by evaluating in double and
-// narrowing (the oracle does the same with libm).
+// Transcendentals: evaluated in double and narrowed, like the oracle does with libm (the stated convention for OpenCL's
+// implementation-defined pow).  CUDA's double pow is accurate to 2 ulp(double), glibc's to < 1, so the narrowed floats
+// agree unless the exact result lies within ~2 ulp(double) of a float rounding boundary: a 2^-27 event per call, i.e.
+// "bit-identical glossy lobes" is a statement with that probability attached, not a proof (pow5 / sqr below are exact
+// products in double and carry no such caveat).  tests/test_gpu_parity.py compares k_display with testkernel.cl and
+// tests/test_gpu_headline.py whole glossy renders bit for bit.
 __device__ __forceinline__ float cr_pow(float x, float y) { return float(pow(double(x), double(y))); }
 __device__ __forceinline__ float cr_pow5(float x) {     // pow(x, 5) for calcFresnel, shade.cl:72
 	double d = double(x), d2 = d * d;

@@ -28,6 +28,7 @@ EXPORTS = [
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
+    "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
 ]
 
 
@@ -119,11 +120,15 @@ class Context:
         self._call("mcpt_synchronize")
 
     # ---- OpenCL::init() pieces
-    def upload_scene(self, triangles, materials, nodes):
+    def upload_scene(self, triangles, materials, nodes, geometry_tag=0):
+        """geometry_tag: the caller's generation counter (non-zero and unchanged = same triangles and nodes as last time)."""
         tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
         mt = np.ascontiguousarray(materials, dtype=T.MATERIAL)
         nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
-        self._call("mcpt_upload_scene", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd))
+        if geometry_tag:
+            self._call("mcpt_upload_scene_tagged", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.c_uint64(geometry_tag))
+        else:
+            self._call("mcpt_upload_scene", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd))
 
     def set_camera(self, camera):
         cam = np.ascontiguousarray(camera, dtype=T.CAMERA)
@@ -222,6 +227,35 @@ class Context:
         out = np.zeros((7, self.npix), np.float64)
         self._call("mcpt_read_sums", _vp(out))
         return out
+
+    def write_sums(self, sums):
+        s = np.ascontiguousarray(sums, dtype=np.float64).reshape(7, self.npix)
+        self._call("mcpt_write_sums", _vp(s))
+
+    def write_history(self, hist, counts):
+        h = np.ascontiguousarray(hist, dtype=np.float32).reshape(self.npix, 4)
+        c = np.ascontiguousarray(counts, dtype=np.int32).reshape(self.npix)
+        self._call("mcpt_write_history", _vp(h), _vp(c))
+
+    def first_sample(self):
+        v = ctypes.c_uint32(0)
+        self._call("mcpt_get_first_sample", ctypes.byref(v))
+        return v.value
+
+    def checkpoint(self):
+        """Everything a later context needs to continue this render bit for bit (see restore)."""
+        hist, counts = self.read_history()
+        return {"hist": hist, "counts": counts, "sums": self.read_sums(), "seeds": self.read_seeds(),
+                "first_sample": np.uint32(self.first_sample()), "size": np.array([self.width, self.height])}
+
+    def restore(self, ck, seed_mode):
+        assert tuple(int(x) for x in ck["size"]) == (self.width, self.height)
+        self.write_history(ck["hist"], ck["counts"])
+        self.write_sums(ck["sums"])
+        if seed_mode == 0:
+            self.write_seeds(ck["seeds"])
+        else:
+            self.set_first_sample(int(ck["first_sample"]))
 
     def bind_sums(self, device_ptr):
         self._call("mcpt_bind_sums", _vp(device_ptr))
