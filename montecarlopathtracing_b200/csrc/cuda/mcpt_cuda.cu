@@ -11,6 +11,8 @@
 #include <thread>
 #include <vector>
 
+#include <cub/device/device_radix_sort.cuh>
+
 #include "mcpt.h"
 #include "accel_build.hpp"
 #include "mcpt_kernels.cuh"
@@ -112,6 +114,21 @@ struct mcpt_ctx {
 		m.emit_tri = emit_tri.p; m.emit_cdf = emit_cdf.p; m.nemit = nemit; m.emit_area = emit_area;
 		return m;
 	}
+	// coherence order of the bounce queues (mcpt_kernels.cuh): keys written by the shade kernel, sorted by CUB, the
+	// resulting permutation read by the next walk
+	bool sort_queues = true;               // env MCPT_SORT=0 switches it off (A/B)
+	DevBuf<uint32_t> sort_keys, sort_keys_out, sort_iota, sort_perm;
+	DevBuf<unsigned char> sort_temp;
+	size_t sort_temp_bytes = 0;
+	// How many items to sort is only known on the device (qcount[d]); CUB wants it on the host.  Any prefix works (see
+	// k_invalidate_keys), so the host uses the live fraction of the same bounce in an EARLIER wave - read back without
+	// ever waiting for the wave being enqueued - plus a margin; until one is known it sorts the whole wave.
+	uint32_t* h_counts = nullptr;          // pinned, 2 slots of (max_depth + 2)
+	cudaEvent_t ev_counts[2] = {nullptr, nullptr};
+	bool slot_pending[2] = {false, false};
+	long slot_total[2] = {0, 0};
+	int next_slot = 0;
+	std::vector<double> live_frac;         // per bounce: live paths / wave paths (1.0 = unknown)
 	DevBuf<uint32_t> rq_count, rq_head;    // per-round counter rings of the regeneration loop (seed_mode 0)
 	DevBuf<int32_t> frames_left;
 	DevBuf<uint32_t> qcount, qhead, first_sample;   // qhead[d]: work-fetch cursor of the persistent bounce d (+1 slot for mcpt_trace)
@@ -135,6 +152,8 @@ struct mcpt_ctx {
 	uint64_t bounce_launches = 0;
 
 	~mcpt_ctx() {
+		for (cudaEvent_t e : ev_counts) if (e) cudaEventDestroy(e);
+		if (h_counts) cudaFreeHost(h_counts);
 		for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
 		if (ev_fork) cudaEventDestroy(ev_fork);
 		for (cudaStream_t g : stream_g) if (g) cudaStreamDestroy(g);
@@ -211,6 +230,24 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 	}
 	CU(c->sample_out.alloc(n));
 	CU(c->hitrec.alloc(n));
+	if (c->sort_queues && c->prm.sampling == MCPT_SAMPLING_REFERENCE && n < (size_t(1) << 31)) {
+		CU(c->sort_keys.alloc(n));
+		CU(c->sort_keys_out.alloc(n));
+		CU(c->sort_iota.alloc(n));
+		CU(c->sort_perm.alloc(n));
+		k_iota<<<blocks(long(n), 256), 256, 0, c->stream>>>(c->sort_iota.p, uint32_t(n));
+		CU(cudaMemsetAsync(c->sort_keys.p, 0xFF, sizeof(uint32_t) * n, c->stream));
+		size_t bytes = 0;
+		CU(cub::DeviceRadixSort::SortPairs(nullptr, bytes, c->sort_keys.p, c->sort_keys_out.p, c->sort_iota.p, c->sort_perm.p,
+		                                   int(n), 0, SORT_KEY_BITS, c->stream));
+		CU(c->sort_temp.alloc(bytes));
+		c->sort_temp_bytes = bytes;
+		if (!c->h_counts) {
+			CU(cudaMallocHost(reinterpret_cast<void**>(&c->h_counts), sizeof(uint32_t) * 2 * (size_t(c->prm.max_depth) + 2)));
+			for (cudaEvent_t& e : c->ev_counts) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+			c->live_frac.assign(size_t(c->prm.max_depth) + 2, 1.0);
+		}
+	}
 	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS) {
 		CU(c->mis_rad.alloc(n)); CU(c->mis_sod.alloc(n)); CU(c->mis_sdp.alloc(n)); CU(c->mis_scon.alloc(n));
 		CU(c->mis_pdf[0].alloc(n)); CU(c->mis_pdf[1].alloc(n)); CU(c->mis_shit.alloc(n));
@@ -234,10 +271,26 @@ int reset_accumulation(mcpt_ctx* c) {
 // One wave of the fused pipeline: nsamples consecutive samples of every pixel.
 int ensure_wide(mcpt_ctx* c);
 
+// Folds the live counts of finished earlier waves into the per-bounce estimates (never waits).
+void poll_live_counts(mcpt_ctx* c) {
+	const int D = c->prm.max_depth;
+	for (int s = 0; s < 2; ++s) {
+		if (!c->slot_pending[s] || cudaEventQuery(c->ev_counts[s]) != cudaSuccess) continue;
+		c->slot_pending[s] = false;
+		const uint32_t* h = c->h_counts + size_t(s) * (size_t(D) + 2);
+		for (int d = 0; d <= D; ++d) c->live_frac[size_t(d)] = double(h[d]) / double(c->slot_total[s]);
+	}
+	(void)cudaGetLastError();       // cudaErrorNotReady from the query is not an error
+}
+
 int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	const int D = c->prm.max_depth;
 	const long total = long(nsamples) * c->npix;
 	WaveDev w = c->wave();
+	// small waves stay unsorted: six more launches per bounce cost more than a few thousand rays gain
+	const bool sorted = c->sort_queues && c->sort_keys.p && c->traversal(c->prm.traversal) == MCPT_TRAVERSAL_FAST &&
+	                    !(c->opt_flags & (2 | 8)) && !c->count_fetches && size_t(total) <= c->sort_keys.n && total >= (1L << 18);
+	if (sorted) poll_live_counts(c);
 	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	CU(cudaMemsetAsync(c->qhead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
@@ -269,6 +322,8 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 			if (c->opt_flags & 8) {        // fused walk + shade in one persistent kernel (the split pipeline measured faster)
 				k_wave_bounce_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, c->qhead.p + d);
 			} else {
+				w.perm = (sorted && d > 0) ? c->sort_perm.p : nullptr;       // primary rays are coherent as generated
+				w.sort_keys = (sorted && d + 1 < D) ? c->sort_keys.p : nullptr;
 				k_wave_trace_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, c->prm.tmin, c->qhead.p + d);
 				if (c->time_bounces) {      // the timed kernel is the walk; the shader runs after the stop event
 					CU(cudaEventRecord(c->ev_pool[c->ev_used + 1], c->stream));
@@ -277,6 +332,15 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 				}
 				k_wave_shade<<<std::min(blocks(total, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, d, D, c->prm.seed_mode);
 				++c->launches;
+				if (w.sort_keys) {
+					// the next bounce's walk order: live items first (their keys are fresh), sorted by coherence key
+					k_invalidate_keys<<<c->nsm * 2, 256, 0, c->stream>>>(c->sort_keys.p, c->qcount.p + d + 1, c->qcount.p + d);
+					long n_est = long(c->live_frac[size_t(d) + 1] * 1.02 * double(total)) + 4096;
+					if (n_est > total) n_est = total;
+					CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->sort_keys.p, c->sort_keys_out.p,
+					                                   c->sort_iota.p, c->sort_perm.p, int(n_est), 0, SORT_KEY_BITS, c->stream));
+					c->launches += 6;       // invalidate + CUB's histogram, exclusive sum and 3 onesweep passes
+				}
 			}
 		}
 		else
@@ -288,6 +352,22 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	}
 	k_wave_resolve<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, nsamples, D, c->prm.max_attempt);
 	c->launches += uint64_t(D) + 2;
+	if (sorted) {
+		// this wave's live counts, for the sort sizes of later waves.  A slot is reused two waves later; by then its copy
+		// has long completed unless the host runs more than a wave ahead, in which case it waits here (never for the
+		// wave it has just enqueued).
+		const int s = c->next_slot;
+		if (c->slot_pending[s]) {
+			CU(cudaEventSynchronize(c->ev_counts[s]));
+			poll_live_counts(c);
+		}
+		CU(cudaMemcpyAsync(c->h_counts + size_t(s) * (size_t(D) + 2), c->qcount.p, sizeof(uint32_t) * (size_t(D) + 1),
+		                   cudaMemcpyDeviceToHost, c->stream));
+		CU(cudaEventRecord(c->ev_counts[s], c->stream));
+		c->slot_pending[s] = true;
+		c->slot_total[s] = total;
+		c->next_slot = s ^ 1;
+	}
 	CU(cudaGetLastError());
 	return MCPT_OK;
 }
@@ -529,6 +609,7 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	c->nsm = prop.multiProcessorCount;
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
 	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128) c->block = b; }
+	if (const char* e = std::getenv("MCPT_SORT")) c->sort_queues = std::atoi(e) != 0;      // development A/B
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
 	ok = ok && c->rays.alloc(n) == cudaSuccess && c->hits.alloc(n) == cudaSuccess && c->closest.alloc(n) == cudaSuccess &&
@@ -876,6 +957,12 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	c->cache_nodes.assign(nodes, nodes + nnodes);
 	c->geometry_tag = tag;
 	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs, have_q ? d_qnodes : nullptr, qframe};
+	for (int a = 0; a < 3; ++a) {
+		const float lo = a == 0 ? nodes[0].bbmin.x : a == 1 ? nodes[0].bbmin.y : nodes[0].bbmin.z;
+		const float hi = a == 0 ? nodes[0].bbmax.x : a == 1 ? nodes[0].bbmax.y : nodes[0].bbmax.z;
+		c->scene.key_lo[a] = lo;
+		c->scene.key_scale[a] = (hi > lo && std::isfinite(32.0f / (hi - lo))) ? 32.0f / (hi - lo) : 0.0f;
+	}
 	c->have_scene = true;
 	return build_emitters(c, tris, ntris, mats);
 }

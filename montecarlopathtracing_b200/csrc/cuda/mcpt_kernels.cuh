@@ -161,6 +161,8 @@ struct WaveDev {
 	unsigned long long* rays_traced;
 	unsigned long long* paths_done;
 	uint32_t* seeds;        // per-pixel persistent LCG state (seed_mode 0)
+	uint32_t* sort_keys;    // coherence key of queue item i of the NEXT bounce, written by the shade kernel (null: queues stay unsorted)
+	const uint32_t* perm;   // walk order of THIS bounce's queue: the walk kernel's i-th ray is item perm[i] (null: identity)
 	float4* hist;
 	int32_t* counts;
 	double* sums;
@@ -284,6 +286,55 @@ __global__ void k_init_seeds(uint32_t* seeds, int n, uint32_t run_seed) {
 
 }  // namespace mcpt
 
+// ================================================================== coherence order of the bounce queues
+// The walk is bound by L1 data-pipe wavefronts (ncu r2a: 90 % of peak): a divergent warp pays one wavefront per lane and
+// load instruction, lanes that fetch the same node share one.  Bounce rays leave the shader in an arbitrary order, so
+// the queue is walked in the order of a 23-bit key - direction on a 16 x 16 octahedral grid (high bits), origin cell on
+// a 32^3 Morton grid (low bits) - found by tools/sort_probe.py to be the best of 40 candidates (x1.56 on the walk of
+// diningroom bounce rays, x1.6 on veach_mis).  Only the ORDER of the walk changes: the shader reads and writes the
+// queue by position as before, so results are bit-identical by construction.
+namespace mcpt {
+constexpr int SORT_KEY_BITS = 24;        // three 8-bit radix passes
+constexpr uint32_t SORT_KEY_INVALID = 0xFFFFFFFFu;
+__device__ __forceinline__ uint32_t spread5(uint32_t v) {       // 5 bits -> every third bit
+	v = (v | (v << 8)) & 0x0000100Fu;
+	v = (v | (v << 4)) & 0x000010C3u;
+	v = (v | (v << 2)) & 0x00001249u;
+	return v;
+}
+__device__ __forceinline__ uint32_t ray_sort_key(const SceneDev& sc, const RayRegs& ray) {
+	const float cx = (ray.origin.x - sc.key_lo[0]) * sc.key_scale[0], cy = (ray.origin.y - sc.key_lo[1]) * sc.key_scale[1],
+	            cz = (ray.origin.z - sc.key_lo[2]) * sc.key_scale[2];
+	const uint32_t qx = uint32_t(fminf(fmaxf(cx, 0.0f), 31.0f)), qy = uint32_t(fminf(fmaxf(cy, 0.0f), 31.0f)),
+	               qz = uint32_t(fminf(fmaxf(cz, 0.0f), 31.0f));
+	const uint32_t cell = spread5(qx) | (spread5(qy) << 1) | (spread5(qz) << 2);
+	// octahedral map of the direction: (u, v) in [-1, 1]^2
+	const float dx = ray.direction.x, dy = ray.direction.y, dz = ray.direction.z;
+	const float inv = rcp_approx(fabsf(dx) + fabsf(dy) + fabsf(dz) + 1e-30f);
+	float u = dx * inv, v = dy * inv;
+	if (dz < 0.0f) {
+		const float uu = copysignf(1.0f - fabsf(v), u), vv = copysignf(1.0f - fabsf(u), v);
+		u = uu; v = vv;
+	}
+	const uint32_t qu = uint32_t(fminf(fmaxf(u * 8.0f + 8.0f, 0.0f), 15.0f)), qv = uint32_t(fminf(fmaxf(v * 8.0f + 8.0f, 0.0f), 15.0f));
+	return (((qu << 4) | qv) << 15) | cell;
+}
+
+// keys[count_next, count_now) <- invalid: those positions held live rays one bounce ago.  Everything from count_now on
+// is invalid already (induction over the bounces; bounce 0 covers the whole wave), so a sort of any prefix of the key
+// array puts exactly the live items first.
+__global__ void __launch_bounds__(256) k_invalidate_keys(uint32_t* __restrict__ keys, const uint32_t* __restrict__ count_next,
+                                                         const uint32_t* __restrict__ count_now) {
+	const uint32_t lo = *count_next, hi = *count_now;
+	for (uint32_t i = lo + blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += gridDim.x * blockDim.x) keys[i] = SORT_KEY_INVALID;
+}
+
+__global__ void k_iota(uint32_t* p, uint32_t n) {
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < n) p[i] = i;
+}
+}  // namespace mcpt
+
 // ================================================================== persistent kernels (MCPT_TRAVERSAL_FAST)
 // Rays of very different traversal length share a warp; with one thread per ray the warp runs until its
 // longest ray is done (measured: 13 of 32 lanes active in the inner loop on incoherent rays).  Here each
@@ -307,7 +358,8 @@ namespace mcpt {
 #define MCPT_REFILL_THRESHOLD 22
 #endif
 
-// Job: bool load(unsigned item, RayRegs&) - false when the item needs no trace (the job has dealt with it);
+// Job: bool load(unsigned& item, RayRegs&) - false when the item needs no trace (the job has dealt with it); may
+//          replace the work index by the queue position it stands for (sorted queues);
 //      void finish(unsigned item, const RayRegs&, const HitRegs&)
 template <class Job>
 __device__ __forceinline__ void persistent_walk(const SceneDev& sc, float tmin, unsigned total, unsigned* head, Job& job) {
@@ -339,7 +391,7 @@ __device__ __forceinline__ void persistent_walk(const SceneDev& sc, float tmin, 
 						const unsigned i = base + unsigned(__popc(m & lt_mask));
 						if (i < total) {
 							item = i;
-							if (job.load(i, ray)) {
+							if (job.load(item, ray)) {
 								walk2_init(w, sc, ray);
 								working = true;
 								want = false;
@@ -367,7 +419,8 @@ struct IntersectJob {
 	const mcpt_ray* rays;
 	mcpt_hit* hits;
 	int32_t* closest;
-	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
+		const unsigned i = item;
 		ray = load_ray(rays, long(i));
 		if (uint32_t(__float_as_int(ray.origin.w)) & MCPT_RAY_TERM_MASK) {      // intersect.cl:16
 			if (closest) closest[i] = -1;
@@ -409,7 +462,8 @@ struct BounceJob {
 	f4 color;
 	uint32_t seed;
 	int path;
-	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
+		const unsigned i = item;
 		float4 o = w.od[src][i], d = w.dp[src][i], c = w.cs[src][i];
 		path = __float_as_int(d.w);
 		ray.origin = ld4(o);
@@ -455,7 +509,9 @@ struct BounceJob {
 struct TraceJob {
 	const WaveDev& w;
 	int src;
-	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
+		if (w.perm) item = __ldcs(w.perm + item);       // walk order -> queue position; finish() writes the record there
+		const unsigned i = item;
 		const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i);
 		ray.origin = ld4(o);
 		ray.direction = f4{d.x, d.y, d.z, 0.0f};
@@ -579,6 +635,7 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 				__stcs(w.od[dst] + pos, st4(ray.origin));
 				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
 				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
+				if (w.sort_keys) w.sort_keys[pos] = ray_sort_key(sc, ray);
 			}
 		}
 #endif

@@ -41,6 +41,7 @@ struct SceneDev {
 	float max_abs;               // largest |coordinate| of the scene's bounding box (finite-arithmetic guard of the fast walk)
 	const QNode* qnodes;         // 15-bit grid version of fast_nodes (null: not available)
 	QFrame qframe;
+	float key_lo[3], key_scale[3];   // sort key of the bounce queues: cell = (origin - key_lo) * key_scale on a 32^3 grid
 };
 
 // 256-bit read-only loads (LDG.E.256, sm_100): a divergent warp costs the L1 one wavefront per lane PER

@@ -111,7 +111,7 @@ def test_converged_cbox_every_pixel_within_4_sigma_and_mre_below_1_percent(cbox)
 
 
 def test_veach_mis_720p_against_the_oracle(mis):
-    w, h, spp, depth = 1280, 720, 4, 16
+    w, h, spp, depth = 1280, 720, 32, 16      # ~1 % of veach_mis's paths reach a lamp: 8 192 paths per block give ~80 counted samples
     O.set_threads()
     ref = _oracle_sums(O.render(mis.camera, w, h, mis.nodes, mis.triangles, mis.materials, depth, 1 << 30, spp, seed_mode=0,
                                 run_seed=77))
@@ -121,8 +121,8 @@ def test_veach_mis_720p_against_the_oracle(mis):
 
     def blocks(s):       # 16x16-pixel block totals of the seven planes
         return s.reshape(7, h // 16, 16, w // 16, 16).sum(axis=(2, 4)).reshape(7, -1)
-    z, _, _, both = _z(blocks(got), blocks(ref), 64)
-    assert both.mean() > 0.5
+    z, _, _, both = _z(blocks(got), blocks(ref), 32)
+    assert both.mean() > 0.3
     assert (z > 4.0).mean() < 2e-3 and z.max() < 7.0, ((z > 4.0).sum(), z.max())
     # pooling ignores that every pixel contributes a fixed number of paths (stratification), so the pooled sigma is an
     # over-estimate wherever a block straddles an edge: only the upper bound is meaningful

@@ -41,8 +41,15 @@ def main():
     n = a.size * a.size
     sums = np.zeros((7, n))
     rays = 0
+    first = 0
+    if os.path.exists(a.out):           # resume: chunk k always uses run_seed + k, so a continued run equals an unbroken one
+        g = np.load(a.out)
+        if (int(g["width"]), int(g["depth"]), int(g["run_seed"])) == (a.size, a.depth, a.run_seed) and \
+                int(g["spp"]) == int(g["chunks"]) * a.spp_per_chunk:
+            sums, rays, first = g["sums"].copy(), int(g["rays_traced"]), int(g["chunks"])
+            print("resuming after chunk %d" % first, flush=True)
     t0 = time.time()
-    for k in range(a.chunks):
+    for k in range(first, a.chunks):
         r = O.render(sc.camera, a.size, a.size, sc.nodes, sc.triangles, sc.materials, a.depth, 1 << 30, a.spp_per_chunk,
                      seed_mode=0, run_seed=a.run_seed + k)
         sums[:3] += r["sum"].T

@@ -66,7 +66,7 @@ def main():
                 ctx.intersect(device.TRAVERSAL_FAST)
                 ctx.shade()
             r = ctx.read_rays()
-            live = (r["state"] & 0xFF000000) == 0 if "state" in r.dtype.names else np.ones(len(r), bool)
+            live = (r["state"].view(np.uint32) & 0xFF000000) == 0
             chunks.append(r[live])
         rays = np.concatenate(chunks)
         n = len(rays)
@@ -98,14 +98,18 @@ def main():
         perm = torch.randperm(n, device="cuda")
         print("%-14s %8.1f Mrays/s" % ("shuffled", n / timed(t[perm].contiguous()) / 1e3))
         keys = {"oct": octant(d)}
-        for b in (3, 4, 5, 6, 7):
-            m = morton(o, lo, hi, b)
-            keys["m%d" % b] = m
-            keys["m%d+oct" % b] = (m << 3) | octant(d)
-            keys["oct+m%d" % b] = (octant(d) << (3 * b)) | m
-        for b, k in ((4, 2), (5, 2), (5, 3), (6, 3), (6, 4)):
-            keys["m%d+d%d" % (b, k)] = (morton(o, lo, hi, b) << (2 * k)) | octa(d, k)
-            keys["d%d+m%d" % (k, b)] = (octa(d, k) << (3 * b)) | morton(o, lo, hi, b)
+        if os.environ.get("PROBE_SET", "1") == "1":
+            for b in (3, 4, 5, 6, 7):
+                m = morton(o, lo, hi, b)
+                keys["m%d" % b] = m
+                keys["m%d+oct" % b] = (m << 3) | octant(d)
+                keys["oct+m%d" % b] = (octant(d) << (3 * b)) | m
+            for b, k in ((4, 2), (5, 2), (5, 3), (6, 3), (6, 4)):
+                keys["m%d+d%d" % (b, k)] = (morton(o, lo, hi, b) << (2 * k)) | octa(d, k)
+                keys["d%d+m%d" % (k, b)] = (octa(d, k) << (3 * b)) | morton(o, lo, hi, b)
+        else:       # direction-major keys of 12..30 bits
+            for k, b in ((3, 3), (4, 3), (4, 4), (4, 5), (5, 3), (5, 4), (5, 5), (6, 4), (6, 6), (4, 6), (5, 6), (7, 5), (8, 4), (6, 0), (8, 0)):
+                keys["d%d+m%d (%d bits)" % (k, b, 2 * k + 3 * b)] = (octa(d, k) << (3 * b)) | (morton(o, lo, hi, b) if b else 0)
         for label, key in keys.items():
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
