@@ -155,6 +155,18 @@ int mcpt_trace_device(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, mcpt_hit* d
 /* instrumented build of the same kernel: counts node and triangle records fetched (device buffers) */
 int mcpt_trace_count(mcpt_ctx* ctx, const mcpt_ray* d_rays, long n, int traversal);
 
+/* Allocation-free variant of mcpt_trace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that must not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same inputs, outputs and results as mcpt_trace(ctx, rays, n, hits, closest, MCPT_TRAVERSAL_FAST) with host
+ * buffers, but the device staging buffers and the walk's work-fetch cursor live in a static device array inside the
+ * library (6.25 MiB, held by every GPU that loads the library until the process exits) instead of cudaMalloc'ed scratch:
+ * the call makes no cudaMalloc / cudaFree / allocating library call.  At most MCPT_TRACE_NOALLOC_MAX_RAYS rays per call
+ * (MCPT_ERR_ARG beyond that, with a message naming the limit).  All calls on a device share the array, which keeps the
+ * last call's contents (the parts that must start at zero are cleared by every call): calls that overlap on the GPU -
+ * two host threads, or two contexts of the same device - race.  Synchronous, like mcpt_trace. */
+#define MCPT_TRACE_NOALLOC_MAX_RAYS 65536
+int mcpt_trace_noalloc(mcpt_ctx* ctx, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_t* closest /* may be NULL */);
+
 /* Measurement aids for bench.py (no effect on results):
  *   count_fetches: the bounce kernels of mcpt_render also count node / triangle records fetched (slower);
  *   time_bounces : CUDA events bracket every bounce-kernel launch on mcpt_stream(ctx); the summed device

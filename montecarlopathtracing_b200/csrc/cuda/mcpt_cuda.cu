@@ -1274,6 +1274,74 @@ int mcpt_trace(mcpt_ctx* c, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_
 	return MCPT_OK;
 }
 
+// ---------------------------------------------------------------- allocation-free variant of mcpt_trace
+// No counterpart in the reference: added for callers that must not call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  mcpt_trace stages the
+// host rays / hits through device scratch it allocates on first use and k_intersect_persistent needs a zeroed
+// work-fetch cursor; here all of that lives in ONE file-scope device array of fixed size, held by every GPU that loads
+// the library until the process exits:
+//   [0, 256)                       the cursor (cleared by every call)
+//   + MAX * 48 B rays, + MAX * 48 B hits (cleared by every call: terminated rays leave their record untouched),
+//   + MAX * 4 B closest-triangle ids
+// Every call on a device shares the array and finds the previous call's contents in it; calls that overlap on the GPU
+// (two host threads, two contexts of one device) race.  Calls are synchronous, so one caller at a time is safe.
+constexpr long NOALLOC_MAX_RAYS = MCPT_TRACE_NOALLOC_MAX_RAYS;
+constexpr size_t NOALLOC_HEADER = 256;
+constexpr size_t NOALLOC_BYTES = NOALLOC_HEADER + size_t(NOALLOC_MAX_RAYS) * (sizeof(mcpt_ray) + sizeof(mcpt_hit) + sizeof(int32_t));
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+// The same walk as k_intersect_persistent, with rays / hits / closest / cursor carved out of the scratch array.
+__global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_intersect_persistent_static(SceneDev sc, unsigned char* scratch, unsigned n, float tmin) {
+	const mcpt_ray* rays = reinterpret_cast<const mcpt_ray*>(scratch + NOALLOC_HEADER);
+	mcpt_hit* hits = reinterpret_cast<mcpt_hit*>(scratch + NOALLOC_HEADER + size_t(NOALLOC_MAX_RAYS) * sizeof(mcpt_ray));
+	int32_t* closest = reinterpret_cast<int32_t*>(scratch + NOALLOC_HEADER + size_t(NOALLOC_MAX_RAYS) * (sizeof(mcpt_ray) + sizeof(mcpt_hit)));
+	IntersectJob job{sc, rays, hits, closest};
+	persistent_walk(sc, tmin, n, reinterpret_cast<unsigned*>(scratch), job);
+}
+
+// Device address of the array on `device` (which must be current): in host code the array's NAME is only a stand-in, a
+// kernel handed it would fault.  Looked up once per device.
+static int noalloc_scratch(int device, unsigned char** out) {
+	static std::mutex m;
+	static unsigned char* table[64] = {};
+	if (device < 0 || device >= 64) return fail(MCPT_ERR_ARG, "mcpt_trace_noalloc: device ordinal out of range");
+	std::lock_guard<std::mutex> lock(m);
+	if (!table[device]) {
+		void* p = nullptr;
+		CU(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+		table[device] = static_cast<unsigned char*>(p);
+	}
+	*out = table[device];
+	return MCPT_OK;
+}
+
+int mcpt_trace_noalloc(mcpt_ctx* c, const mcpt_ray* rays, long n, mcpt_hit* hits, int32_t* closest) {
+	if (int r = check_ctx(c, true, false)) return r;          // cudaSetDevice(ctx device): the lookup below needs it current
+	if (n < 0 || (n > 0 && (!rays || !hits))) return fail(MCPT_ERR_ARG, "mcpt_trace_noalloc: bad arguments");
+	if (n > NOALLOC_MAX_RAYS)
+		return fail(MCPT_ERR_ARG, "mcpt_trace_noalloc: " + std::to_string(n) + " rays exceed the maximum of " +
+		            std::to_string(NOALLOC_MAX_RAYS) + " per call (MCPT_TRACE_NOALLOC_MAX_RAYS; use mcpt_trace or split the batch)");
+	if (n == 0) return MCPT_OK;
+	unsigned char* scratch = nullptr;
+	if (int r = noalloc_scratch(c->prm.device, &scratch)) return r;
+	mcpt_ray* d_rays = reinterpret_cast<mcpt_ray*>(scratch + NOALLOC_HEADER);
+	mcpt_hit* d_hits = reinterpret_cast<mcpt_hit*>(scratch + NOALLOC_HEADER + size_t(NOALLOC_MAX_RAYS) * sizeof(mcpt_ray));
+	int32_t* d_closest = reinterpret_cast<int32_t*>(scratch + NOALLOC_HEADER + size_t(NOALLOC_MAX_RAYS) * (sizeof(mcpt_ray) + sizeof(mcpt_hit)));
+	CU(cudaMemsetAsync(scratch, 0, NOALLOC_HEADER, c->stream));                       // the cursor starts at zero
+	CU(cudaMemsetAsync(d_hits, 0, sizeof(mcpt_hit) * size_t(n), c->stream));            // no stale records of the last call
+	CU(cudaMemcpyAsync(d_rays, rays, sizeof(mcpt_ray) * size_t(n), cudaMemcpyHostToDevice, c->stream));
+	if (c->force_reference)      // scene the product walk cannot take (boxes not nested): the reference-order kernel, same scratch
+		k_intersect<MCPT_TRAVERSAL_REFERENCE, false><<<blocks(n, 128), 128, 0, c->stream>>>(c->scene, d_rays, n, c->prm.tmin, d_hits, d_closest, nullptr);
+	else
+		k_intersect_persistent_static<<<std::min(blocks(n, 128), c->persistent_grid(128)), 128, 0, c->stream>>>(c->scene, scratch, unsigned(n), c->prm.tmin);
+	++c->launches;
+	CU(cudaGetLastError());
+	CU(cudaMemcpyAsync(hits, d_hits, sizeof(mcpt_hit) * size_t(n), cudaMemcpyDeviceToHost, c->stream));
+	if (closest) CU(cudaMemcpyAsync(closest, d_closest, sizeof(int32_t) * size_t(n), cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
 int mcpt_set_profiling(mcpt_ctx* c, int count_fetches, int time_bounces) {
 	if (int r = check_ctx(c, false, false)) return r;
 	CU(cudaStreamSynchronize(c->stream));

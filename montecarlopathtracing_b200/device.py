@@ -29,7 +29,9 @@ EXPORTS = [
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
     "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
+    "mcpt_trace_noalloc",
 ]
+TRACE_NOALLOC_MAX_RAYS = 65536        # MCPT_TRACE_NOALLOC_MAX_RAYS of include/mcpt.h
 
 
 class Params(ctypes.Structure):
@@ -270,6 +272,19 @@ class Context:
         if closest is None:
             closest = np.zeros(n, np.int32)
         self._call("mcpt_trace", _vp(r), ctypes.c_long(n), _vp(hits), _vp(closest), traversal)
+        return hits, closest
+
+    def trace_noalloc(self, rays, hits=None, closest=None):
+        """mcpt_trace_noalloc: the product walk on host rays with the device scratch in a static array of the library
+        (no cudaMalloc inside the call); at most TRACE_NOALLOC_MAX_RAYS rays."""
+        r = rays if (isinstance(rays, np.ndarray) and rays.dtype == T.RAY and rays.flags.c_contiguous) \
+            else np.ascontiguousarray(rays, dtype=T.RAY)
+        n = len(r)
+        if hits is None:
+            hits = np.zeros(n, T.HIT)
+        if closest is None:
+            closest = np.zeros(n, np.int32)
+        self._call("mcpt_trace_noalloc", _vp(r), ctypes.c_long(n), _vp(hits), _vp(closest))
         return hits, closest
 
     def trace_device(self, d_rays, n, d_hits, d_closest=None, traversal=TRAVERSAL_FAST):
