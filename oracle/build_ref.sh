@@ -47,3 +47,27 @@ for k in rayGenerator intersect shade history testkernel EPO; do
 done
 g++ -std=gnu++17 -O2 -fPIC -fopenmp -ffp-contract=off -w -I"$HERE" -I"$OUT/src" -shared -o "$OUT/libmcpt_refcl.so" "$HERE/ref_kernels.cpp"
 echo "build_ref: wrote $OUT/libmcpt_refcl.so"
+
+# ---- the drop-in proof: integration/OpenCLApp_mcpt.cpp compiled against the reference's OWN
+# config.cpp, thirdpartywrapper.cpp, auxiliary.cpp, BVH/*.cpp, tinyobj and stb, linked with libmcpt_cuda.so, driven by a
+# headless main that loops update().  tests/test_gpu_dropin.py runs it on the GPU box (prebuilt binary travels there).
+ROOT="$(cd "$HERE/.." && pwd)"
+PKG="$ROOT/montecarlopathtracing_b200"
+if [ -e "$PKG/libmcpt_cuda.so" ]; then
+  printf '#include <cmath>\n#include <cfloat>\n#include <cstdint>\n#include <cstring>\n#include <deque>\n#include <functional>\n#include <queue>\n#include <unordered_set>\n#include <iostream>\n#undef M_PI\n' > "$OUT/src/prelude.h"
+  DROPFLAGS="$CXXFLAGS -I$ROOT/include -include $OUT/src/prelude.h"
+  OBJS=""
+  for f in config thirdpartywrapper auxiliary BVH/bvh BVH/treeletBVH; do
+    o="$OUT/dropin_$(basename $f).o"
+    g++ $DROPFLAGS -c "$REF/$f.cpp" -o "$o"
+    OBJS="$OBJS $o"
+  done
+  g++ $DROPFLAGS -c "$OUT/src/hlbvh_patched.cpp" -o "$OUT/dropin_hlbvh.o"
+  for f in OpenCLApp_mcpt headless_main oclbasic_stub; do
+    g++ $DROPFLAGS -c "$ROOT/integration/$f.cpp" -o "$OUT/dropin_$f.o"
+    OBJS="$OBJS $OUT/dropin_$f.o"
+  done
+  g++ -o "$OUT/mcpt_dropin" $OBJS "$OUT/dropin_hlbvh.o" "$OUT/tiny_obj_loader.o" "$OUT/stb_image_write.o" $OCL \
+      -L"$PKG" -lmcpt_cuda -Wl,-rpath,'$ORIGIN/../../montecarlopathtracing_b200'
+  echo "build_ref: wrote $OUT/mcpt_dropin"
+fi
