@@ -102,6 +102,18 @@ int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const
  * CL_MEM_COPY_HOST_PTR buffers, oclbasic.h:56-58) without comparing 80 MB to find that out.  Tag 0 = no promise. */
 int mcpt_upload_scene_tagged(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                              const mcpt_bvh_node* nodes, int nnodes, uint64_t geometry_tag);
+/* Scene cache support (the reference derives nothing ahead of time - its kernels walk the uploaded
+ * BVHNode[] directly, scenebuild.cpp:97-100).  mcpt_derive_scene runs the host part of mcpt_upload_scene (validation,
+ * leaf records, two-box nodes, the binned-SAH tree of the fast walk) without a context or a GPU and returns it as one
+ * relocatable blob (release with mcpt_free_blob) that mcpt_host_cache_store keeps next to the arrays.
+ * mcpt_upload_scene_derived uploads with such a blob instead of deriving again: the blob is accepted only if its content
+ * hash matches these very triangles and nodes, it was written by this library version and every link in it is in
+ * range (MCPT_ERR_ARG otherwise - the caller then falls back to mcpt_upload_scene); results are identical. */
+int mcpt_derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                      const mcpt_bvh_node* nodes, int nnodes, void** blob, size_t* bytes);
+void mcpt_free_blob(void* blob);
+int mcpt_upload_scene_derived(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                              const mcpt_bvh_node* nodes, int nnodes, const void* blob, size_t bytes, uint64_t geometry_tag);
 int mcpt_set_camera(mcpt_ctx* ctx, const mcpt_camera* cam);
 
 /* ---- stage level: one call = one reference kernel over the W*H work items (reference buffer layouts) ---- */

@@ -11,6 +11,7 @@
  *   mcpt_host_sah           <- BVH::TEST::SAH                     bvhtest.cpp:104-115
  *   mcpt_host_parse_camera  <- Auxiliary::parseCamera             auxiliary.cpp:20-71
  *   mcpt_host_load_config   <- Config::CONFIG                     config.cpp:70-125
+ *   mcpt_host_cache_*       (new: what loadObject + the BVH build produce, kept on disk)
  *   mcpt_host_write_hdr     <- ThirdPartyWrapper::outputPicture   thirdpartywrapper.cpp:14-23
  *   mcpt_host_write_png     (new: gamma 1/2.2 8-bit view of the same buffer, testkernel.cl:9-14)
  *
@@ -21,6 +22,7 @@
 #ifndef MCPT_HOST_H
 #define MCPT_HOST_H
 
+#include <stddef.h>
 #include "mcpt_types.h"
 
 #ifdef __cplusplus
@@ -52,6 +54,23 @@ int mcpt_host_load_object(const char* directory, const char* objname, int with_n
 int mcpt_host_load_object_mt(const char* directory, const char* objname, int with_normals, int threads,
                              mcpt_triangle** tris, int* ntris, mcpt_material** mats, int* nmats,
                              int** material_ids);
+/* SURVEY §8 f-2, binary scene cache.  The reference parses the OBJ and rebuilds the BVH on every start
+ * (thirdpartywrapper.cpp:25-99, scenebuild.cpp:50-101); these four calls keep that work in one file per scene:
+ *   key   = content hash of the OBJ, of every MTL file it names, of `bvhtype`, with_normals and the record layouts;
+ *   path  = "<directory><objname>.<bvhtype>.mcptcache" (under $MCPT_CACHE_DIR when that is set);
+ *   store = Triangle[] / Material[] / material ids / BVHNode[] + an opaque blob (the traversal layout of
+ *           mcpt_derive_scene, libmcpt_cuda), written to a temporary name and renamed;
+ *   load  = 0 and malloc'ed copies of the same bytes on a hit; 1 on a miss (absent, other version, stale key,
+ *           truncated or checksum mismatch - reason in mcpt_host_last_error()); negative on error. */
+typedef struct mcpt_scene_key { uint64_t h[2]; } mcpt_scene_key;
+int mcpt_host_scene_key(const char* directory, const char* objname, const char* bvhtype, int with_normals, mcpt_scene_key* key);
+int mcpt_host_cache_path(const char* directory, const char* objname, const char* bvhtype, char* out, size_t cap);
+int mcpt_host_cache_store(const char* path, const mcpt_scene_key* key, const mcpt_triangle* tris, int ntris,
+                          const mcpt_material* mats, int nmats, const int* material_ids, const mcpt_bvh_node* nodes,
+                          int nnodes, const void* derived, size_t derived_bytes);
+int mcpt_host_cache_load(const char* path, const mcpt_scene_key* key, mcpt_triangle** tris, int* ntris,
+                         mcpt_material** mats, int* nmats, int** material_ids, mcpt_bvh_node** nodes, int* nnodes,
+                         void** derived /* may be NULL */, size_t* derived_bytes /* may be NULL */);
 /* out_nodes must hold 2*n-1 nodes; returns the node count. bvhtype: "hlbvh" | "treelet" | "treeletGPU" */
 int mcpt_host_build_bvh(const mcpt_triangle* tris, int n, const char* bvhtype, mcpt_bvh_node* out_nodes);
 int mcpt_host_treelet(const mcpt_bvh_node* nodes_in, int nn, mcpt_bvh_node* out_nodes);

@@ -14,6 +14,7 @@
 #include <cub/device/device_radix_sort.cuh>
 
 #include "mcpt.h"
+#include "../common/hash128.hpp"
 #include "accel_build.hpp"
 #include "mcpt_kernels.cuh"
 #include "mcpt_mis.cuh"
@@ -812,8 +813,146 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 	return MCPT_OK;
 }
 
+// ---- the derived layout as a relocatable blob (scene cache): header | DLeaf[ntris] | DNode[ndn] | DNode[nfast]
+struct DerivedHeader {
+	char magic[8];
+	uint32_t version, sizeof_dnode, sizeof_dleaf, builder_id;
+	int32_t ntris, nnodes, nmats, contained, fast_depth, pad;
+	uint64_t ndn, nfast;
+	uint64_t input_hash[2];      // of the Triangle[] and BVHNode[] bytes the layout was derived from
+};
+static_assert(sizeof(DerivedHeader) == 80, "DerivedHeader");
+constexpr char DERIVED_MAGIC[8] = {'M', 'C', 'P', 'T', 'D', 'R', 'V', '1'};
+constexpr uint32_t DERIVED_VERSION = 1;
+
+static Hash128 geometry_hash(const mcpt_triangle* tris, int ntris, const mcpt_bvh_node* nodes, int nnodes) {
+	Hash128 h;
+	hash_update(h, tris, sizeof(mcpt_triangle) * size_t(ntris));
+	hash_update(h, nodes, sizeof(mcpt_bvh_node) * size_t(nnodes));
+	return h;
+}
+
+static size_t derived_blob_bytes(const DerivedScene& d) {
+	return sizeof(DerivedHeader) + d.dt.size() * sizeof(DLeaf) + (d.dn.size() + d.fast.size()) * sizeof(DNode);
+}
+
+static void write_derived_blob(const DerivedScene& d, int nnodes, const Hash128& geom, unsigned char* out) {
+	DerivedHeader h{};
+	std::memcpy(h.magic, DERIVED_MAGIC, 8);
+	h.version = DERIVED_VERSION;
+	h.sizeof_dnode = sizeof(DNode);
+	h.sizeof_dleaf = sizeof(DLeaf);
+	h.builder_id = FAST_TREE_BUILDER_ID;
+	h.ntris = int32_t(d.dt.size());
+	h.nnodes = nnodes;
+	h.nmats = d.nmats;
+	h.contained = d.contained ? 1 : 0;
+	h.fast_depth = d.fast_depth;
+	h.ndn = d.dn.size();
+	h.nfast = d.fast.size();
+	h.input_hash[0] = geom.a; h.input_hash[1] = geom.b;
+	std::memcpy(out, &h, sizeof(h));
+	out += sizeof(h);
+	std::memcpy(out, d.dt.data(), d.dt.size() * sizeof(DLeaf));
+	out += d.dt.size() * sizeof(DLeaf);
+	std::memcpy(out, d.dn.data(), d.dn.size() * sizeof(DNode));
+	out += d.dn.size() * sizeof(DNode);
+	std::memcpy(out, d.fast.data(), d.fast.size() * sizeof(DNode));
+}
+
+// Accepts a blob only if it was derived from exactly these triangles and nodes (content hash) by this library version,
+// and if every index in it stays inside its array: the walk kernels follow child links without bounds checks.
+static int read_derived_blob(const void* blob, size_t bytes, const mcpt_triangle* tris, int ntris, int nmats,
+                             const mcpt_bvh_node* nodes, int nnodes, DerivedScene& out) {
+	if (!blob || bytes < sizeof(DerivedHeader)) return fail(MCPT_ERR_ARG, "derived layout: blob too small");
+	DerivedHeader h;
+	std::memcpy(&h, blob, sizeof(h));
+	if (std::memcmp(h.magic, DERIVED_MAGIC, 8) != 0 || h.version != DERIVED_VERSION || h.sizeof_dnode != sizeof(DNode) ||
+	    h.sizeof_dleaf != sizeof(DLeaf) || h.builder_id != FAST_TREE_BUILDER_ID)
+		return fail(MCPT_ERR_ARG, "derived layout: written by another library version");
+	if (h.ntris != ntris || h.nnodes != nnodes || h.nmats != nmats) return fail(MCPT_ERR_ARG, "derived layout: belongs to another scene (counts differ)");
+	const bool root_leaf = nodes[0].left == nodes[0].right;
+	const uint64_t want_dn = root_leaf ? 1 : uint64_t(nnodes), want_fast = uint64_t(std::max(1, ntris - 1));
+	if (h.ndn != want_dn || h.nfast != want_fast ||
+	    bytes != sizeof(DerivedHeader) + uint64_t(ntris) * sizeof(DLeaf) + (h.ndn + h.nfast) * sizeof(DNode))
+		return fail(MCPT_ERR_ARG, "derived layout: section sizes do not match the scene");
+	const Hash128 geom = geometry_hash(tris, ntris, nodes, nnodes);
+	if (geom.a != h.input_hash[0] || geom.b != h.input_hash[1])
+		return fail(MCPT_ERR_ARG, "derived layout: stale (triangles or nodes changed since it was derived)");
+	const unsigned char* p = static_cast<const unsigned char*>(blob) + sizeof(DerivedHeader);
+	out.dt.resize(size_t(ntris));
+	std::memcpy(out.dt.data(), p, out.dt.size() * sizeof(DLeaf));
+	p += out.dt.size() * sizeof(DLeaf);
+	out.dn.resize(size_t(h.ndn));
+	std::memcpy(out.dn.data(), p, out.dn.size() * sizeof(DNode));
+	p += out.dn.size() * sizeof(DNode);
+	out.fast.resize(size_t(h.nfast));
+	std::memcpy(out.fast.data(), p, out.fast.size() * sizeof(DNode));
+	out.contained = h.contained != 0;
+	out.fast_depth = h.fast_depth;
+	out.nmats = nmats;
+	for (int i = 0; i < ntris; ++i)
+		if (out.dt[size_t(i)].rank < 0 || out.dt[size_t(i)].rank >= ntris || out.dt[size_t(i)].material < 0 || out.dt[size_t(i)].material >= nmats)
+			return fail(MCPT_ERR_ARG, "derived layout: leaf record out of range");
+	if (!root_leaf) {
+		// reference-topology nodes: inner slots only (leaf slots stay zero); fast tree: preorder, so a child's index
+		// exceeds its parent's (no cycles) and every triangle hangs below exactly one link
+		auto ref_ok = [&](int32_t r, int64_t lo, int64_t hi) { return r < 0 ? ~r < ntris : (r > lo && r < hi); };
+		for (int i = 0; i < nnodes; ++i) {
+			if (nodes[i].left == nodes[i].right) continue;
+			const DNode& d = out.dn[size_t(i)];
+			if (!ref_ok(d.left, -1, nnodes) || !ref_ok(d.right, -1, nnodes)) return fail(MCPT_ERR_ARG, "derived layout: node link out of range");
+		}
+		std::vector<char> seen(size_t(ntris), 0);
+		long leaves = 0;
+		for (size_t i = 0; i < out.fast.size(); ++i) {
+			for (int32_t r : {out.fast[i].left, out.fast[i].right}) {
+				if (!ref_ok(r, int64_t(i), int64_t(out.fast.size()))) return fail(MCPT_ERR_ARG, "derived layout: fast-tree link out of range");
+				if (r < 0) {
+					if (seen[size_t(~r)]) return fail(MCPT_ERR_ARG, "derived layout: triangle linked twice");
+					seen[size_t(~r)] = 1;
+					++leaves;
+				}
+			}
+		}
+		if (leaves != ntris) return fail(MCPT_ERR_ARG, "derived layout: fast tree does not reach every triangle");
+		if (h.fast_depth < 1 || h.fast_depth > ntris) return fail(MCPT_ERR_ARG, "derived layout: implausible depth");
+	}
+	return MCPT_OK;
+}
+
 static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
-                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag);
+                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag, const void* blob = nullptr, size_t blob_bytes = 0);
+
+static int check_scene_args(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats, const mcpt_bvh_node* nodes, int nnodes) {
+	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
+		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
+	return MCPT_OK;
+}
+
+int mcpt_derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats, const mcpt_bvh_node* nodes,
+                      int nnodes, void** blob, size_t* bytes) {
+	if (!blob || !bytes) return fail(MCPT_ERR_ARG, "mcpt_derive_scene: null output");
+	if (int r = check_scene_args(tris, ntris, mats, nmats, nodes, nnodes)) return r;
+	DerivedScene d;
+	if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, d)) return r;
+	d.nmats = nmats;
+	const size_t n = derived_blob_bytes(d);
+	unsigned char* out = static_cast<unsigned char*>(std::malloc(n));
+	if (!out) return fail(MCPT_ERR_ARG, "mcpt_derive_scene: out of host memory");
+	write_derived_blob(d, nnodes, geometry_hash(tris, ntris, nodes, nnodes), out);
+	*blob = out;
+	*bytes = n;
+	return MCPT_OK;
+}
+
+void mcpt_free_blob(void* blob) { std::free(blob); }
+
+int mcpt_upload_scene_derived(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                              const mcpt_bvh_node* nodes, int nnodes, const void* blob, size_t bytes, uint64_t geometry_tag) {
+	if (!blob || bytes == 0) return fail(MCPT_ERR_ARG, "mcpt_upload_scene_derived: null blob");
+	return upload_scene(c, tris, ntris, mats, nmats, nodes, nnodes, geometry_tag, blob, bytes);
+}
 
 int mcpt_upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes) {
@@ -826,10 +965,17 @@ int mcpt_upload_scene_tagged(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, 
 }
 
 static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
-                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag) {
+                        const mcpt_bvh_node* nodes, int nnodes, uint64_t tag, const void* blob, size_t blob_bytes) {
 	if (int r = check_ctx(c, false, false)) return r;
-	if (!tris || !mats || !nodes || ntris <= 0 || nmats <= 0 || nnodes != 2 * ntris - 1)
-		return fail(MCPT_ERR_ARG, "mcpt_upload_scene: expected ntris > 0, nmats > 0 and nnodes == 2*ntris-1");
+	if (int r = check_scene_args(tris, ntris, mats, nmats, nodes, nnodes)) return r;
+	// ---- a layout derived earlier (scene cache): validated against these very arrays before anything else, never trusted
+	std::shared_ptr<DerivedScene> from_blob;
+	if (blob) {
+		from_blob = std::make_shared<DerivedScene>();
+		if (int r = read_derived_blob(blob, blob_bytes, tris, ntris, nmats, nodes, nnodes, *from_blob)) return r;
+		for (int i = 0; i < ntris; ++i)
+			if (tris[i].material_id < 0 || tris[i].material_id >= nmats) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
+	}
 	// ---- unchanged geometry (same bytes as the previous upload): the derived layout on the device is still
 	// valid; only the caller's arrays are copied again (what OpenCL's CL_MEM_COPY_HOST_PTR upload would do)
 	// A non-zero geometry_tag equal to the previous upload's is the caller's word that triangles and nodes are the same
@@ -863,8 +1009,9 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 		    bytes_equal(g_derived->nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)) {
 			derived = g_derived;
 		} else {
-			auto fresh = std::make_shared<DerivedScene>();
-			if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, *fresh)) return r;
+			auto fresh = from_blob ? from_blob : std::make_shared<DerivedScene>();
+			if (!from_blob)
+				if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, *fresh)) return r;
 			fresh->tris.assign(tris, tris + ntris);
 			fresh->nodes.assign(nodes, nodes + nnodes);
 			fresh->nmats = nmats;

@@ -73,6 +73,23 @@ Scene load_object(const std::string& directory, const std::string& objname, bool
 // Same result, parsed by `threads` threads (0 = all hardware threads, 1 = the serial loader above).
 Scene load_object_parallel(const std::string& directory, const std::string& objname, bool with_normals, int threads);
 
+// ------------------------------------------------------------------ binary scene cache
+// One file per (OBJ + MTL content, bvhtype): the loader's and the BVH builder's outputs plus an opaque blob holding the
+// traversal layout libmcpt_cuda derives from them (mcpt_derive_scene).  scene_cache.cpp.
+struct SceneKey { uint64_t h[2]; };
+struct CachedScene {
+	std::vector<mcpt_triangle> triangles;
+	std::vector<mcpt_material> materials;
+	std::vector<int> material_ids;
+	std::vector<mcpt_bvh_node> nodes;
+	std::vector<unsigned char> derived;
+	bool with_normals = true;
+};
+SceneKey scene_key(const std::string& directory, const std::string& objname, const std::string& bvhtype, bool with_normals);
+std::string scene_cache_path(const std::string& directory, const std::string& objname, const std::string& bvhtype);
+void scene_cache_store(const std::string& path, const SceneKey& key, const CachedScene& scene);      // throws on I/O errors
+bool scene_cache_load(const std::string& path, const SceneKey& key, CachedScene& scene, std::string* why_not = nullptr);
+
 // ------------------------------------------------------------------ BVH
 // LBVH (BVH/hlbvh.cpp:92-200): 30-bit Morton of AABB centroids, stable sort, split at the
 // highest differing bit, node numbering internal 0..N-2 / leaves N-1..2N-2.  memcmp-equal to the

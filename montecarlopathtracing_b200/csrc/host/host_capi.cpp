@@ -58,6 +58,65 @@ int mcpt_host_load_object_mt(const char* directory, const char* objname, int wit
 	});
 }
 
+int mcpt_host_scene_key(const char* directory, const char* objname, const char* bvhtype, int with_normals, mcpt_scene_key* key) {
+	return guarded([&] {
+		SceneKey k = scene_key(directory, objname, bvhtype ? bvhtype : "hlbvh", with_normals != 0);
+		key->h[0] = k.h[0]; key->h[1] = k.h[1];
+		return 0;
+	});
+}
+
+int mcpt_host_cache_path(const char* directory, const char* objname, const char* bvhtype, char* out, size_t cap) {
+	return guarded([&] {
+		std::string p = scene_cache_path(directory, objname, bvhtype ? bvhtype : "hlbvh");
+		if (p.size() + 1 > cap) throw std::runtime_error("mcpt_host_cache_path: buffer too small");
+		std::memcpy(out, p.c_str(), p.size() + 1);
+		return 0;
+	});
+}
+
+int mcpt_host_cache_store(const char* path, const mcpt_scene_key* key, const mcpt_triangle* tris, int ntris,
+                          const mcpt_material* mats, int nmats, const int* material_ids, const mcpt_bvh_node* nodes,
+                          int nnodes, const void* derived, size_t derived_bytes) {
+	return guarded([&] {
+		if (!path || !key || !tris || ntris <= 0 || (nmats > 0 && !mats) || !material_ids || (nnodes > 0 && !nodes) ||
+		    (derived_bytes > 0 && !derived))
+			throw std::runtime_error("mcpt_host_cache_store: null argument");
+		CachedScene s;
+		s.triangles.assign(tris, tris + ntris);
+		s.materials.assign(mats, mats + nmats);
+		s.material_ids.assign(material_ids, material_ids + ntris);
+		s.nodes.assign(nodes, nodes + nnodes);
+		const unsigned char* d = static_cast<const unsigned char*>(derived);
+		s.derived.assign(d, d + derived_bytes);
+		scene_cache_store(path, SceneKey{{key->h[0], key->h[1]}}, s);
+		return 0;
+	});
+}
+
+int mcpt_host_cache_load(const char* path, const mcpt_scene_key* key, mcpt_triangle** tris, int* ntris,
+                         mcpt_material** mats, int* nmats, int** material_ids, mcpt_bvh_node** nodes, int* nnodes,
+                         void** derived, size_t* derived_bytes) {
+	return guarded([&] {
+		CachedScene s;
+		std::string why;
+		if (!scene_cache_load(path, SceneKey{{key->h[0], key->h[1]}}, s, &why)) {
+			g_err = why;
+			return 1;
+		}
+		*ntris = int(s.triangles.size());
+		*nmats = int(s.materials.size());
+		*nnodes = int(s.nodes.size());
+		*tris = dup(s.triangles);
+		*mats = dup(s.materials);
+		*material_ids = dup(s.material_ids);
+		*nodes = dup(s.nodes);
+		if (derived) *derived = dup(s.derived);
+		if (derived_bytes) *derived_bytes = s.derived.size();
+		return 0;
+	});
+}
+
 int mcpt_host_build_bvh(const mcpt_triangle* tris, int n, const char* bvhtype, mcpt_bvh_node* out_nodes) {
 	return guarded([&] {
 		std::vector<mcpt_triangle> t(tris, tris + n);

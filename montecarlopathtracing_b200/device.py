@@ -29,7 +29,7 @@ EXPORTS = [
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
     "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
-    "mcpt_trace_noalloc",
+    "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived",
 ]
 TRACE_NOALLOC_MAX_RAYS = 65536        # MCPT_TRACE_NOALLOC_MAX_RAYS of include/mcpt.h
 
@@ -122,12 +122,17 @@ class Context:
         self._call("mcpt_synchronize")
 
     # ---- OpenCL::init() pieces
-    def upload_scene(self, triangles, materials, nodes, geometry_tag=0):
-        """geometry_tag: the caller's generation counter (non-zero and unchanged = same triangles and nodes as last time)."""
+    def upload_scene(self, triangles, materials, nodes, geometry_tag=0, derived=None):
+        """geometry_tag: the caller's generation counter (non-zero and unchanged = same triangles and nodes as last time).
+        derived: a blob of derive_scene() for these very arrays (scene cache): uploaded instead of deriving again."""
         tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
         mt = np.ascontiguousarray(materials, dtype=T.MATERIAL)
         nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
-        if geometry_tag:
+        if derived is not None:
+            blob = np.frombuffer(derived, dtype=np.uint8)
+            self._call("mcpt_upload_scene_derived", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), _vp(blob),
+                       ctypes.c_size_t(blob.size), ctypes.c_uint64(geometry_tag))
+        elif geometry_tag:
             self._call("mcpt_upload_scene_tagged", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.c_uint64(geometry_tag))
         else:
             self._call("mcpt_upload_scene", _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd))
@@ -318,6 +323,24 @@ def image_from_sums(sums, width, height):
     img = np.zeros((height, width, 4), np.float32)
     img[..., :3] = (sums[:3] / n).T.reshape(height, width, 3)
     return img
+
+
+def derive_scene(triangles, materials, nodes):
+    """The traversal layout mcpt_upload_scene derives on the host (leaf records, two-box nodes, the binned-SAH tree of
+    the fast walk) as one relocatable blob (bytes) - what the scene cache stores next to the arrays.  Needs no GPU."""
+    tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
+    mt = np.ascontiguousarray(materials, dtype=T.MATERIAL)
+    nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    blob, n = ctypes.c_void_p(), ctypes.c_size_t()
+    L = lib()
+    L.mcpt_free_blob.restype = None
+    L.mcpt_free_blob.argtypes = [ctypes.c_void_p]
+    if L.mcpt_derive_scene(_vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.byref(blob), ctypes.byref(n)) != 0:
+        raise McptError("mcpt_derive_scene: %s" % L.mcpt_last_error().decode())
+    try:
+        return ctypes.string_at(blob, n.value)
+    finally:
+        L.mcpt_free_blob(blob)
 
 
 def build_lbvh(triangles, device=0, return_ms=False):

@@ -35,6 +35,7 @@ def lib():
         L = ctypes.CDLL(path)
         L.mcpt_host_last_error.restype = ctypes.c_char_p
         L.mcpt_host_sah.restype = ctypes.c_double
+        L.mcpt_host_free.argtypes = [ctypes.c_void_p]
         _LIB = L
     return _LIB
 
@@ -73,6 +74,66 @@ def load_object(directory, objname, with_normals=True, threads=1):
     finally:
         L.mcpt_host_free(tr); L.mcpt_host_free(mt); L.mcpt_host_free(ids)
     return Scene(tris, mats, mids)
+
+
+class SceneKey(ctypes.Structure):
+    _fields_ = [("h", ctypes.c_uint64 * 2)]
+
+
+def scene_key(directory, objname, bvhtype="hlbvh", with_normals=True):
+    """Content hash of the OBJ, of every MTL file it names, of bvhtype and of the record layouts (scene cache key)."""
+    k = SceneKey()
+    _check(lib().mcpt_host_scene_key(directory.encode(), objname.encode(), bvhtype.encode(), int(with_normals), ctypes.byref(k)))
+    return (int(k.h[0]), int(k.h[1]))
+
+
+def cache_path(directory, objname, bvhtype="hlbvh"):
+    buf = ctypes.create_string_buffer(1024)
+    _check(lib().mcpt_host_cache_path(directory.encode(), objname.encode(), bvhtype.encode(), buf, ctypes.c_size_t(1024)))
+    return buf.value.decode()
+
+
+def cache_store(path, key, scene, nodes, derived=b""):
+    """scene: Scene (triangles, materials, material_ids); nodes: BVHNode[]; derived: device.derive_scene() blob."""
+    tr = np.ascontiguousarray(scene.triangles, dtype=T.TRIANGLE)
+    mt = np.ascontiguousarray(scene.materials, dtype=T.MATERIAL)
+    ids = np.ascontiguousarray(scene.material_ids, dtype=np.int32)
+    nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
+    k = SceneKey((ctypes.c_uint64 * 2)(*key))
+    blob = np.frombuffer(derived, dtype=np.uint8) if len(derived) else None
+    _check(lib().mcpt_host_cache_store(path.encode(), ctypes.byref(k), tr.ctypes.data_as(ctypes.c_void_p), len(tr),
+                                       mt.ctypes.data_as(ctypes.c_void_p), len(mt), ids.ctypes.data_as(ctypes.c_void_p),
+                                       nd.ctypes.data_as(ctypes.c_void_p), len(nd),
+                                       blob.ctypes.data_as(ctypes.c_void_p) if blob is not None else None,
+                                       ctypes.c_size_t(len(derived))))
+
+
+def cache_load(path, key):
+    """(Scene, nodes, derived bytes) on a hit, None on a miss (absent / stale / other version / corrupt)."""
+    L = lib()
+    tr, mt, nd, dv = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+    ids = ctypes.POINTER(ctypes.c_int)()
+    nt, nm, nn, nb = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_size_t()
+    k = SceneKey((ctypes.c_uint64 * 2)(*key))
+    rc = _check(L.mcpt_host_cache_load(path.encode(), ctypes.byref(k), ctypes.byref(tr), ctypes.byref(nt), ctypes.byref(mt),
+                                       ctypes.byref(nm), ctypes.byref(ids), ctypes.byref(nd), ctypes.byref(nn),
+                                       ctypes.byref(dv), ctypes.byref(nb)))
+    if rc == 1:
+        return None
+    try:
+        tris = np.frombuffer(ctypes.string_at(tr, nt.value * 64), dtype=T.TRIANGLE).copy()
+        mats = np.frombuffer(ctypes.string_at(mt, nm.value * 48), dtype=T.MATERIAL).copy()
+        mids = np.frombuffer(ctypes.string_at(ids, nt.value * 4), dtype=np.int32).copy()
+        nodes = np.frombuffer(ctypes.string_at(nd, nn.value * 64), dtype=T.BVH_NODE).copy()
+        derived = ctypes.string_at(dv, nb.value)
+    finally:
+        for p in (tr, mt, ids, nd, dv):
+            L.mcpt_host_free(p)
+    return Scene(tris, mats, mids), nodes, derived
+
+
+def cache_miss_reason():
+    return lib().mcpt_host_last_error().decode()
 
 
 def build_bvh(triangles, bvhtype="hlbvh"):

@@ -138,3 +138,45 @@ def test_sample_sharding_is_refused_in_reference_seeding(cbox):
         ctx.set_first_sample(0)
         with pytest.raises(device.McptError, match="seed_mode 0"):
             ctx.set_first_sample(5)
+
+
+def test_upload_with_a_cached_layout_equals_a_fresh_upload(cbox, mis):
+    """SURVEY §8 f-2 (scene cache): mcpt_upload_scene_derived with the blob of mcpt_derive_scene gives the context the
+    same device layout as mcpt_upload_scene - hits and rendered sums equal bit for bit - and refuses blobs that belong
+    to other geometry or carry out-of-range links."""
+    from tests.util import random_rays
+    w, h = 96, 64
+    blob = device.derive_scene(cbox.triangles, cbox.materials, cbox.nodes)
+    rays = random_rays(50_000, cbox.nodes)
+    kw = dict(max_depth=8, max_attempt=1 << 20, seed_mode=1, run_seed=5, samples_in_flight=4)
+    with _ctx(cbox, w, h, **kw) as a:
+        hits_a, closest_a = a.trace(rays)
+        a.render(6)
+        sums_a = a.read_sums()
+    with device.Context(w, h, **kw) as b:
+        b.upload_scene(cbox.triangles, cbox.materials, cbox.nodes, derived=blob)
+        b.set_camera(cbox.camera)
+        hits_b, closest_b = b.trace(rays)
+        b.render(6)
+        assert hit_mismatches(hits_a, hits_b) == 0 and np.array_equal(closest_a, closest_b)
+        assert b.read_sums().tobytes() == sums_a.tobytes()
+        # other geometry (a node box moved by one ulp): the content hash no longer matches
+        moved = cbox.nodes.copy()
+        moved["bbmax"][5][0] = np.nextafter(moved["bbmax"][5][0], np.float32(np.inf))
+        with pytest.raises(device.McptError, match="stale"):
+            b.upload_scene(cbox.triangles, cbox.materials, moved, derived=blob)
+        with pytest.raises(device.McptError, match="another scene"):
+            b.upload_scene(mis.triangles, mis.materials, mis.nodes, derived=blob)
+        # a link of the fast tree bent out of range (header | DLeaf[n] | DNode[2n-1] | DNode[n-1]: left is word 12 of a node)
+        n = len(cbox.triangles)
+        bent = bytearray(blob)
+        off = 80 + 96 * n + 64 * (2 * n - 1) + 64 * 7 + 48
+        bent[off:off + 4] = np.int32(n + 12345).tobytes()
+        with pytest.raises(device.McptError, match="out of range|twice|reach"):
+            b.upload_scene(cbox.triangles, cbox.materials, cbox.nodes, derived=bytes(bent))
+        with pytest.raises(device.McptError, match="too small|version"):
+            b.upload_scene(cbox.triangles, cbox.materials, cbox.nodes, derived=b"garbage" * 20)
+        # the refused uploads left the context as it was
+        b.reset_accumulation()
+        b.render(6)
+        assert b.read_sums().tobytes() == sums_a.tobytes()
