@@ -56,6 +56,7 @@ struct State {
 	uint32_t run_seed = 1;
 	bool reference_seeding = true;
 	bool mis = false;        // --mis: NEE + MIS sampling mode (same image, far less variance; needs order-independent seeds)
+	bool mis_ratio = false;  // --mis-ratio: as --mis, with the denominator P(sample != 0) estimated by NEE + MIS as well
 	bool host_bvh = false;   // --host-bvh: build the LBVH with the kept host code instead of the device builder
 	bool overlap_init = false;   // --overlap-init (multi-GPU): every device starts rendering as soon as IT is ready
 	double first_ready_s = 0.0, all_ready_s = 0.0;
@@ -105,7 +106,7 @@ mcpt_ctx* make_context(const State& s, int g, int ngpus) {
 	p.max_attempt = s.cfg.attempt;
 	p.device = g;
 	p.seed_mode = (ngpus > 1 || !s.reference_seeding || s.mis) ? 1 : 0;
-	p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
+	p.sampling = s.mis ? (s.mis_ratio ? MCPT_SAMPLING_NEE_MIS_RATIO : MCPT_SAMPLING_NEE_MIS) : MCPT_SAMPLING_REFERENCE;
 	p.run_seed = s.run_seed;
 	p.traversal = MCPT_TRAVERSAL_FAST;
 	mcpt_ctx* c = mcpt_create(&p);
@@ -196,7 +197,7 @@ void write_checkpoint(const State& s, const std::string& file, int frames_done) 
 	std::memcpy(h.magic, "MCPTCKP1", 8);
 	h.width = s.cfg.width; h.height = s.cfg.height; h.maxdepth = s.cfg.maxdepth;
 	h.seed_mode = (!s.reference_seeding || s.mis) ? 1 : 0;
-	h.run_seed = s.run_seed; h.frames_done = uint32_t(frames_done); h.sampling = s.mis ? 1u : 0u;
+	h.run_seed = s.run_seed; h.frames_done = uint32_t(frames_done); h.sampling = s.mis ? (s.mis_ratio ? 2u : 1u) : 0u;
 	if (mcpt_read_history(c, hist.data(), counts.data()) || mcpt_read_sums(c, sums.data()) || mcpt_read_seeds(c, seeds.data()) ||
 	    mcpt_get_first_sample(c, &h.first_sample))
 		die("checkpoint", mcpt_last_error());
@@ -224,7 +225,7 @@ int read_checkpoint(State& s, const std::string& file) {
 	if (std::fread(&h, sizeof(h), 1, f) != 1 || std::memcmp(h.magic, "MCPTCKP1", 8) != 0) die("resume", "not a checkpoint file");
 	const int seed_mode = (!s.reference_seeding || s.mis) ? 1 : 0;
 	if (h.width != s.cfg.width || h.height != s.cfg.height || h.maxdepth != s.cfg.maxdepth || h.seed_mode != seed_mode ||
-	    h.run_seed != s.run_seed || h.sampling != (s.mis ? 1u : 0u))
+	    h.run_seed != s.run_seed || h.sampling != (s.mis ? (s.mis_ratio ? 2u : 1u) : 0u))
 		die("resume", "checkpoint was written with another size, depth, seed or seeding / sampling mode");
 	const bool ok = std::fread(hist.data(), sizeof(float), hist.size(), f) == hist.size() && std::fread(counts.data(), sizeof(int32_t), npix, f) == npix &&
 	                std::fread(sums.data(), sizeof(double), sums.size(), f) == sums.size() && std::fread(seeds.data(), sizeof(uint32_t), npix, f) == npix;
@@ -333,7 +334,7 @@ void run_processes(State& s, int procs, int frames, std::chrono::steady_clock::t
 			setenv("CUDA_VISIBLE_DEVICES", dev.c_str(), 1);
 			mcpt_params p{};
 			p.width = s.cfg.width; p.height = s.cfg.height; p.max_depth = s.cfg.maxdepth; p.max_attempt = s.cfg.attempt;
-			p.device = 0; p.seed_mode = 1; p.sampling = s.mis ? MCPT_SAMPLING_NEE_MIS : MCPT_SAMPLING_REFERENCE;
+			p.device = 0; p.seed_mode = 1; p.sampling = s.mis ? (s.mis_ratio ? MCPT_SAMPLING_NEE_MIS_RATIO : MCPT_SAMPLING_NEE_MIS) : MCPT_SAMPLING_REFERENCE;
 			p.run_seed = s.run_seed; p.traversal = MCPT_TRAVERSAL_FAST;
 			mcpt_ctx* c = mcpt_create(&p);
 			if (!c) bail("mcpt_create", mcpt_last_error());
@@ -409,13 +410,14 @@ int main(int argc, char** argv) {
 		else if (a == "--order-independent-seeds") s.reference_seeding = false;
 		else if (a == "--host-bvh") s.host_bvh = true;
 		else if (a == "--mis") s.mis = true;
+		else if (a == "--mis-ratio") s.mis = s.mis_ratio = true;
 		else if (a == "--overlap-init") s.overlap_init = true;
 		else if (a == "--no-cache") s.use_cache = false;
 		else if (a == "--checkpoint") checkpoint_file = next();
 		else if (a == "--checkpoint-every") checkpoint_every = std::atoi(next());
 		else if (a == "--resume") resume_file = next();
 		else if (a == "--stop-after") stop_after = std::atoi(next());      // leave after this many frames (an interrupted run)
-		else die("unknown option (use --config --configid --gpus --procs --spp --out --seed --batch --order-independent-seeds --host-bvh --mis --overlap-init --no-cache --checkpoint --checkpoint-every --resume --stop-after)", a.c_str());
+		else die("unknown option (use --config --configid --gpus --procs --spp --out --seed --batch --order-independent-seeds --host-bvh --mis --mis-ratio --overlap-init --no-cache --checkpoint --checkpoint-every --resume --stop-after)", a.c_str());
 	}
 	if (mcpt_host_load_config(config.c_str(), configid, &s.cfg) < 0) die("config", mcpt_host_last_error());
 	if (s.cfg.testall) {                                     // main.cpp:12-15 -> BVH::TEST::testall(), bvhtest.cpp:615-650
@@ -477,6 +479,7 @@ int main(int argc, char** argv) {
 			pid_t pid = fork();
 			if (pid < 0) die("--procs", "fork failed");
 			if (pid == 0) {
+				setenv("CUDA_VISIBLE_DEVICES", visible_device(0).c_str(), 1);     // the device builders run on the first device
 				State h = s;
 				load_scene(h);
 				_exit(std::strcmp(h.cache_state, "miss") == 0 ? 0 : 3);

@@ -72,7 +72,9 @@ typedef struct mcpt_params {
 	                             results come from mcpt_read_sums (sum / count), history stays untouched */
 	int reserved[5];
 } mcpt_params;
-enum { MCPT_SAMPLING_REFERENCE = 0, MCPT_SAMPLING_NEE_MIS = 1 };
+/* MCPT_SAMPLING_NEE_MIS_RATIO (2): as NEE_MIS, and plane 6 of the sums holds an NEE + MIS estimate of the expected number
+ * of counted samples instead of the raw count (whose binomial noise otherwise dominates the image), mcpt_mis.cuh */
+enum { MCPT_SAMPLING_REFERENCE = 0, MCPT_SAMPLING_NEE_MIS = 1, MCPT_SAMPLING_NEE_MIS_RATIO = 2 };
 
 typedef struct mcpt_stats {
 	uint64_t rays_traced;     /* live rays that entered an intersect stage since create/reset (Mrays/s numerator) */
@@ -185,6 +187,19 @@ int mcpt_trace_noalloc(mcpt_ctx* ctx, const mcpt_ray* rays, long n, mcpt_hit* hi
  *                  time and launch count since the last call are returned by mcpt_get_bounce_time. */
 int mcpt_set_profiling(mcpt_ctx* ctx, int count_fetches, int time_bounces);
 int mcpt_get_bounce_time(mcpt_ctx* ctx, double* ms, uint64_t* launches);
+
+/* Checked build (-DMCPT_CHECKED=1; tools/checked_run.sh): every node, leaf, stack, permutation, queue and path index the
+ * kernels follow is compared with its bound before use; violations are counted and the first one recorded.
+ * out4 = {failures, code of the first (CHK_* in mcpt_traverse.cuh), its value, its bound} for kernels run on `device`
+ * so far.  The product build has no such checks and returns MCPT_ERR_STATE.  (compute-sanitizer is closed on the GPU
+ * pool this was developed on; the checked build run over tools/sanitize_targets.py is what stands in for it.) */
+int mcpt_check_failures(int device, uint64_t* out4);
+
+/* NEE + MIS mode (MCPT_SAMPLING_NEE_MIS), test aid: the tabulated acceptance probability of the glossy lobe's rejection
+ * loop (shade.cl:130-132) against angle(mirror direction, normal), MCPT_PHONG_ACCEPT_POINTS values uniform in [0, pi/2],
+ * as the kernels interpolate it (mcpt_device.cuh).  Host only, needs no context. */
+#define MCPT_PHONG_ACCEPT_POINTS 1025
+int mcpt_phong_accept_table(float* out, int n);
 
 /* Streaming-read bandwidth (GB/s, best of 5) of a scratch buffer of `bytes` read `iters` times on `device`:
  * 32 MiB measures the L2 ceiling the walk's node fetches live under, several GiB the HBM ceiling.  Needs no context. */

@@ -2,7 +2,7 @@
  *
  * Every struct is BYTE-IDENTICAL to the record of the same name in the reference's
  * MonteCarloPathTracing/objdef.h:21-99 (sizes checked by static_assert below and against the
- * reference's own headers in tests/test_layout.py), so a reference-side caller can hand its
+ * reference's own headers in tests/test_host.py and tests/test_abi.py), so a reference-side caller can hand its
  * std::vector<Triangle>/<Material>/<BVHNode> storage to the C ABI unchanged.
  *
  *   reference type   objdef.h    size   notes

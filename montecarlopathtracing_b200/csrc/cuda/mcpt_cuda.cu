@@ -65,6 +65,44 @@ struct DevBuf {
 
 }  // namespace
 
+// Acceptance probability of the glossy lobe's rejection loop (shade.cl:130-132) against theta = angle(mirror direction,
+// normal), PHONG_ACCEPT_N + 1 points uniform in [0, pi/2]: the share of randomDirection's density about r that lies
+// above the surface.  randomDirection draws u = k / 32768 and a uniform azimuth; a direction at polar angle alpha(u)
+// about r is above the horizon for the azimuth fraction 1 (cot alpha cot theta >= 1) or acos(-cot alpha cot theta) / pi.
+// Summed over the reference's own 32 768 values of u, once per process.
+const std::vector<float>& phong_accept_table() {
+	static std::vector<float> tab;
+	static std::once_flag once;
+	std::call_once(once, [] {
+		constexpr int NU = 32768;
+		std::vector<double> cot_alpha(NU);
+		for (int k = 0; k < NU; ++k) {
+			const double u = double(k) / NU, D = 1.0 - u + u * u;
+			const double ca = (1.0 - u) / std::sqrt(D), sa = std::sqrt(std::max(0.0, 1.0 - ca * ca));
+			cot_alpha[size_t(k)] = sa > 0.0 ? ca / sa : 1e300;
+		}
+		tab.assign(size_t(PHONG_ACCEPT_N) + 1, 1.0f);
+		const unsigned nt = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+		std::vector<std::thread> th;
+		for (unsigned t = 0; t < nt; ++t)
+			th.emplace_back([&, t] {
+				for (int j = int(t); j <= PHONG_ACCEPT_N; j += int(nt)) {
+					const double theta = 1.57079632679489661923 * double(j) / PHONG_ACCEPT_N;
+					const double ct = std::cos(theta), st = std::sin(theta);
+					const double cot_theta = st > 0.0 ? ct / st : 1e300;
+					double acc = 0.0;
+					for (int k = 0; k < NU; ++k) {
+						const double x = cot_alpha[size_t(k)] * cot_theta;
+						acc += x >= 1.0 ? 1.0 : std::acos(-x) / 3.14159265358979323846;
+					}
+					tab[size_t(j)] = float(acc / NU);
+				}
+			});
+		for (auto& x : th) x.join();
+	});
+	return tab;
+}
+
 struct mcpt_ctx {
 	mcpt_params prm{};
 	cudaStream_t stream = nullptr;
@@ -101,7 +139,7 @@ struct mcpt_ctx {
 	DevBuf<float2> hitrec;
 	// NEE + MIS mode
 	DevBuf<float4> mis_rad, mis_sod, mis_sdp, mis_scon;
-	DevBuf<float> mis_pdf[2], emit_cdf;
+	DevBuf<float> mis_pdf[2], emit_cdf, phong_accept, mis_den, mis_sden;
 	DevBuf<float2> mis_shit;
 	DevBuf<uint32_t> mis_scount, mis_shead;
 	DevBuf<int32_t> emit_tri;
@@ -113,6 +151,8 @@ struct mcpt_ctx {
 		m.sod = mis_sod.p; m.sdp = mis_sdp.p; m.scon = mis_scon.p; m.shit = mis_shit.p;
 		m.scount = mis_scount.p;
 		m.emit_tri = emit_tri.p; m.emit_cdf = emit_cdf.p; m.nemit = nemit; m.emit_area = emit_area;
+		m.phong_accept = phong_accept.p;
+		m.den = mis_den.p; m.sden = mis_sden.p;
 		return m;
 	}
 	// coherence order of the bounce queues (mcpt_kernels.cuh): keys written by the shade kernel, sorted by CUB, the
@@ -189,6 +229,7 @@ struct mcpt_ctx {
 		w.counts = counts.p;
 		w.sums = sums;
 		w.npix = npix;
+		w.capacity = uint32_t(std::min<size_t>(od[0].n, 0xffffffffu));
 		return w;
 	}
 	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
@@ -249,9 +290,15 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 			c->live_frac.assign(size_t(c->prm.max_depth) + 2, 1.0);
 		}
 	}
-	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS) {
+	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE) {
+		if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS_RATIO) { CU(c->mis_den.alloc(n)); CU(c->mis_sden.alloc(n)); }
 		CU(c->mis_rad.alloc(n)); CU(c->mis_sod.alloc(n)); CU(c->mis_sdp.alloc(n)); CU(c->mis_scon.alloc(n));
 		CU(c->mis_pdf[0].alloc(n)); CU(c->mis_pdf[1].alloc(n)); CU(c->mis_shit.alloc(n));
+		if (!c->phong_accept.p) {
+			const std::vector<float>& tab = phong_accept_table();
+			CU(c->phong_accept.alloc(tab.size()));
+			CU(cudaMemcpyAsync(c->phong_accept.p, tab.data(), sizeof(float) * tab.size(), cudaMemcpyHostToDevice, c->stream));
+		}
 	}
 	c->wave_samples = samples;
 	return MCPT_OK;
@@ -526,6 +573,7 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 	CU(cudaMemsetAsync(c->mis_shead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	CU(cudaMemsetAsync(c->mis_rad.p, 0, sizeof(float4) * size_t(total), c->stream));
 	CU(cudaMemsetAsync(c->mis_pdf[0].p, 0, sizeof(float) * size_t(total), c->stream));
+	if (c->mis_den.p) CU(cudaMemsetAsync(c->mis_den.p, 0, sizeof(float) * size_t(total), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int BS = 128;
 	const int pg = std::min(blocks(total, BS), c->persistent_grid(BS));
@@ -596,12 +644,12 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	c->prm = *params;
 	if (c->prm.tmin == 0.0f) c->prm.tmin = 0.001f;
 	if (c->prm.seed_mode == 0) c->prm.samples_in_flight = 1;
-	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE && c->prm.sampling != MCPT_SAMPLING_NEE_MIS) {
+	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE && c->prm.sampling != MCPT_SAMPLING_NEE_MIS && c->prm.sampling != MCPT_SAMPLING_NEE_MIS_RATIO) {
 		fail(MCPT_ERR_ARG, "mcpt_create: unknown sampling mode");
 		delete c;
 		return nullptr;
 	}
-	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS && c->prm.seed_mode != 1) {
+	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE && c->prm.seed_mode != 1) {
 		fail(MCPT_ERR_ARG, "mcpt_create: MCPT_SAMPLING_NEE_MIS needs seed_mode 1 (it renders in waves of whole samples)");
 		delete c;
 		return nullptr;
@@ -1206,7 +1254,7 @@ int mcpt_frame(mcpt_ctx* c) {
 int mcpt_render_async(mcpt_ctx* c, int spp) {
 	if (int r = check_ctx(c, true, true)) return r;
 	if (spp < 0) return fail(MCPT_ERR_ARG, "mcpt_render: negative spp");
-	if (c->prm.sampling == MCPT_SAMPLING_NEE_MIS && (c->force_reference || c->scene.root_is_leaf))
+	if (c->prm.sampling != MCPT_SAMPLING_REFERENCE && (c->force_reference || c->scene.root_is_leaf))
 		return fail(MCPT_ERR_STATE, "mcpt_render: the NEE + MIS mode needs the fast walk, which this scene cannot use (single triangle or boxes not nested)");
 	int S = c->prm.seed_mode == 0 ? 1 : c->prm.samples_in_flight;
 	if (S <= 0) {
@@ -1231,7 +1279,7 @@ int mcpt_render_async(mcpt_ctx* c, int spp) {
 	if (int r = ensure_wave(c, S)) return r;
 	for (int done = 0; done < spp;) {
 		int s = spp - done < S ? spp - done : S;
-		if (int r = (c->prm.sampling == MCPT_SAMPLING_NEE_MIS ? enqueue_wave_mis(c, s) : enqueue_wave(c, s))) return r;
+		if (int r = (c->prm.sampling != MCPT_SAMPLING_REFERENCE ? enqueue_wave_mis(c, s) : enqueue_wave(c, s))) return r;
 		done += s;
 	}
 	return MCPT_OK;
@@ -1486,6 +1534,28 @@ int mcpt_trace_noalloc(mcpt_ctx* c, const mcpt_ray* rays, long n, mcpt_hit* hits
 	CU(cudaMemcpyAsync(hits, d_hits, sizeof(mcpt_hit) * size_t(n), cudaMemcpyDeviceToHost, c->stream));
 	if (closest) CU(cudaMemcpyAsync(closest, d_closest, sizeof(int32_t) * size_t(n), cudaMemcpyDeviceToHost, c->stream));
 	CU(cudaStreamSynchronize(c->stream));
+	return MCPT_OK;
+}
+
+int mcpt_check_failures(int device, uint64_t* out4) {
+#if MCPT_CHECKED
+	if (!out4) return fail(MCPT_ERR_ARG, "mcpt_check_failures: null output");
+	unsigned long long h[4] = {0, 0, 0, 0};
+	CU(cudaSetDevice(device));
+	CU(cudaDeviceSynchronize());
+	CU(cudaMemcpyFromSymbol(h, g_check, sizeof(h)));
+	for (int k = 0; k < 4; ++k) out4[k] = h[k];
+	return MCPT_OK;
+#else
+	(void)device; (void)out4;
+	return fail(MCPT_ERR_STATE, "mcpt_check_failures: this is the product build (bounds checks are compiled in with -DMCPT_CHECKED=1, tools/checked_run.sh)");
+#endif
+}
+
+int mcpt_phong_accept_table(float* out, int n) {
+	const std::vector<float>& tab = phong_accept_table();
+	if (!out || n != int(tab.size())) return fail(MCPT_ERR_ARG, "mcpt_phong_accept_table: expected a buffer of " + std::to_string(tab.size()) + " floats");
+	std::memcpy(out, tab.data(), sizeof(float) * tab.size());
 	return MCPT_OK;
 }
 

@@ -233,7 +233,9 @@ __device__ __forceinline__ void finish_phong(f4& color, float p, float post) { c
 __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
                                           RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
                                           uint32_t& seed_slot, int max_depth, bool* diffuse_lobe = nullptr,
-                                          PhongDefer* defer = nullptr) {
+                                          PhongDefer* defer = nullptr, f4* phong_axis = nullptr) {
+	// phong_axis (NEE + MIS mode): receives the mirror direction with w = 1 when the glossy lobe was taken, else w = 0
+	if (phong_axis) *phong_axis = f4{0, 0, 0, 0};
 	if (diffuse_lobe) *diffuse_lobe = false;
 	if (defer) defer->pending = false;
 	const uint32_t state = uint32_t(__float_as_int(ray.origin.w));
@@ -265,6 +267,7 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		} else if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
 		else color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
 		if (diffuse_lobe) *diffuse_lobe = !specular;
+		if (phong_axis && specular) *phong_axis = f4{axis.x, axis.y, axis.z, 1.0f};
 		seed_slot = seed;
 	} else
 	switch (mat.type) {
@@ -315,6 +318,20 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 // c = (1-u)/sqrt(D), D = 1 - u + u^2, and p = |du/dc| / (2 pi) = D^(3/2) / (pi (1 + u)); inverting c(u) gives
 // 1 - u = 2c / (c + sqrt(4 - 3 c^2)) (the cancellation-free form of SURVEY's expression).  The reference's u and
 // phi live on 2^15-point grids; the continuous density is their limit (relative difference ~1e-4).
+// Glossy lobe (shade.cl:125-147): randomDirection about the mirror direction r, redrawn until the direction lies above
+// the surface.  Its density is random_direction_pdf(cos(d, r)) / A on the upper hemisphere of n, A(theta) = the loop's
+// acceptance probability = the share of the lobe above the horizon, a function of theta = angle(r, n) alone
+// (A(0) = 1, A(pi/2) = 1/2).  The host tabulates it (PHONG_ACCEPT_N + 1 points, uniform in theta, summed over the
+// reference's own 2^15 values of u with the azimuth integrated in closed form); linear interpolation error < 1e-6.
+constexpr int PHONG_ACCEPT_N = 1024;
+__device__ __forceinline__ float phong_accept_probability(const float* __restrict__ tab, float cos_rn) {
+	const float theta = acosf(fminf(fmaxf(cos_rn, 0.0f), 1.0f));
+	const float x = theta * (float(PHONG_ACCEPT_N) / 1.57079632679f);
+	const int i = min(int(x), PHONG_ACCEPT_N - 1);
+	const float a = __ldg(tab + i), b = __ldg(tab + i + 1);
+	return a + (b - a) * (x - float(i));
+}
+
 __device__ __forceinline__ float random_direction_pdf(float c) {
 	if (!(c > 0.0f)) return 0.0f;
 	c = fminf(c, 1.0f);

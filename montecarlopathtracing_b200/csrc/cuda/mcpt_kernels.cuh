@@ -163,6 +163,7 @@ struct WaveDev {
 	uint32_t* seeds;        // per-pixel persistent LCG state (seed_mode 0)
 	uint32_t* sort_keys;    // coherence key of queue item i of the NEXT bounce, written by the shade kernel (null: queues stay unsorted)
 	const uint32_t* perm;   // walk order of THIS bounce's queue: the walk kernel's i-th ray is item perm[i] (null: identity)
+	uint32_t capacity;      // items every queue buffer holds (checked build: bound of queue positions and path ids)
 	float4* hist;
 	int32_t* counts;
 	double* sums;
@@ -509,8 +510,10 @@ struct BounceJob {
 struct TraceJob {
 	const WaveDev& w;
 	int src;
+	unsigned total;         // items in this bounce's queue (bound of the permutation's entries in the checked build)
 	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
 		if (w.perm) item = __ldcs(w.perm + item);       // walk order -> queue position; finish() writes the record there
+		MCPT_CHECK_INDEX(CHK_PERM, item, total);
 		const unsigned i = item;
 		const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i);
 		ray.origin = ld4(o);
@@ -524,7 +527,7 @@ struct TraceJob {
 
 __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_trace_persistent(SceneDev sc, WaveDev w, int depth, float tmin, unsigned* head) {
 	const unsigned total = w.qcount[depth];
-	TraceJob job{w, depth & 1};
+	TraceJob job{w, depth & 1, total};
 	persistent_walk(sc, tmin, total, head, job);
 }
 
@@ -556,6 +559,7 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 			const float t = hr.x;
 			const int closest = __float_as_int(hr.y);
 			path = __float_as_int(d.w);
+			MCPT_CHECK_INDEX(CHK_PATH, path, w.capacity);
 			const int pixel = path % w.npix;
 			ray.origin = ld4(o);
 			ray.direction = f4{d.x, d.y, d.z, __int_as_float(pixel)};
@@ -631,7 +635,8 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 			if (lane == 0) qb = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(mask)));
 			qb = __shfl_sync(0xffffffffu, qb, 0);
 			if (alive) {
-				const uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+				uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
+				MCPT_CHECK_INDEX(CHK_QUEUE, pos, w.capacity);
 				__stcs(w.od[dst] + pos, st4(ray.origin));
 				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
 				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));

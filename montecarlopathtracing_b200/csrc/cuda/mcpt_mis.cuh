@@ -13,14 +13,24 @@
 //   random_direction_pdf), (b) a point sampled uniformly by area on the emitter triangles (solid-angle density
 //   q = d^2 / (|cos_l| A)).  The reference's per-bounce factor is w_ref = Kd cos / (2 pi) (shade.cl:120) applied
 //   to directions of density p_ref, i.e. it integrates g = p_ref * w_ref; technique (b) therefore contributes
-//   T * g(w) Le / (p_ref + q) and technique (a) T * w_ref Le * p_ref / (p_ref + q).  Specular glossy lobes and
-//   glass keep the reference's estimator (weight 1).
+//   T * g(w) Le / (p_ref + q) and technique (a) T * w_ref Le * p_ref / (p_ref + q).
+// * The glossy lobe (shade.cl:125-147) is treated the same way: its directions have density
+//   p_lobe = p_ref(cos(d, r)) / A(angle(r, n)) above the surface (r = mirror direction, A = acceptance probability of
+//   the reference's rejection loop, tabulated: phong_accept_probability) and carry the weight
+//   w = ks pow(cos(d, r), Ns) cos(d, n) / (2 pi) (shade.cl:141-143).  Glass is a delta BSDF: no NEE through it.
 // * A shadow ray counts only if its CLOSEST hit (same tie semantics as everywhere: the product walk) is the
 //   sampled triangle itself, which is what "first emitter seen in that direction" means to the chain.
 // * Emitters radiate from both sides and without a cosine at the light, like shade.cl:155-158.
 // Output: per pixel sum of the numerator over ALL samples and the count of samples with X != 0 - the same
 // seven planes as the reference-faithful mode (mcpt_read_sums); image = sum / count.  hist/count (the running
 // mean of history.cl) cannot express a ratio of sums and are left untouched.
+// * MCPT_SAMPLING_NEE_MIS_RATIO estimates the DENOMINATOR the same way.  The raw count is a sum of Bernoulli(P) draws
+//   (relative noise sqrt((1 - P) / (N P)), P = 2 % on cbox) and dominates the image noise once the numerator is
+//   well estimated.  P(X != 0) = sum over vertices of P(the next hit is an emitter and the sample value is non-zero),
+//   an integral of the same form with Le replaced by the indicator [|X(w)| != 0] (history.cl:10, evaluated on the
+//   value the chain would have produced in that direction): technique (a) adds the MIS weight whenever the chain
+//   reaches an emitter with X != 0, technique (b) adds indicator * p / (p + q) for unoccluded emitter samples.  Plane
+//   6 then holds the sum of these estimates (not an integer); the chain - and therefore what (a) sees - is unchanged.
 #pragma once
 #include "mcpt_kernels.cuh"
 
@@ -32,9 +42,12 @@ struct MisDev {
 	float4* sod;            // shadow rays of the current bounce: origin
 	float4* sdp;            //   direction + path id
 	float4* scon;           //   contribution if unoccluded (rgb) + sampled emitter triangle
+	float* den;             // ratio mode, per path: estimate of P(X != 0) so far (null in MCPT_SAMPLING_NEE_MIS)
+	float* sden;            // ratio mode, per shadow ray: its share of that estimate if unoccluded
 	float2* shit;           //   hit record written by the walk
 	uint32_t* scount;       // scount[d] = shadow rays emitted at bounce d
 	const int32_t* emit_tri;
+	const float* phong_accept;   // acceptance probability of the glossy lobe's rejection loop (mcpt_device.cuh)
 	const float* emit_cdf;  // inclusive, normalised
 	int nemit;
 	float emit_area;
@@ -80,6 +93,7 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 		int path = 0;
 		float pdf_next = 0.0f;
 		float4 s_o, s_d, s_c;
+		float s_den = 0.0f;
 		if (i < total) {
 			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
 			const float2 hr = __ldcs(w.hitrec + i);
@@ -108,7 +122,10 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 			}
 			uint32_t nee_rng = seed ^ 0xA511E9B3u;            // before the chain advances the LCG
 			bool diffuse_lobe = false;
-			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, &diffuse_lobe);
+			f4 phong_axis;
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, &diffuse_lobe, nullptr, &phong_axis);
+			const bool phong_lobe = phong_axis.w != 0.0f;
+			const float accept = phong_lobe ? phong_accept_probability(m.phong_accept, dot3(phong_axis, nn)) : 1.0f;
 			float4 rad = m.rad[path];
 			if (closest >= 0 && mtype == MCPT_LIGHT) {
 				// technique (a): the chain reached an emitter; `color` is the reference's sample value X
@@ -119,13 +136,18 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 					wgt = pdf_prev / (pdf_prev + q);
 				}
 				rad.x += color.x * wgt; rad.y += color.y * wgt; rad.z += color.z * wgt;
-				if (sqrtf(dot4(color, color)) != 0.0f) rad.w = 1.0f;      // history.cl:10 - the reference's own test (squares may underflow)
+				if (sqrtf(dot4(color, color)) != 0.0f) {                   // history.cl:10 - the reference's own test (squares may underflow)
+					rad.w = 1.0f;
+					if (m.den) m.den[path] += wgt;
+				}
 				m.rad[path] = rad;
 			}
 			if (!alive) {
+				if (m.den) rad.w = m.den[path];                            // ratio mode: plane 6 accumulates the estimate of P(X != 0)
 				__stcs(w.sample_out + path, rad);
-			} else if (diffuse_lobe) {
-				pdf_next = random_direction_pdf(dot3(ray.direction, nn));
+			} else if (diffuse_lobe || phong_lobe) {
+				const f4 axis = phong_lobe ? f4{phong_axis.x, phong_axis.y, phong_axis.z, 0.0f} : nn;
+				pdf_next = random_direction_pdf(dot3(ray.direction, axis)) / accept;
 				if (m.nemit > 0) {
 					// technique (b): one emitter point, uniform by area
 					const float r0 = u01(nee_rng), r1 = u01(nee_rng), r2 = u01(nee_rng);
@@ -144,15 +166,24 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 						const f4 wdir{wv.x / dist, wv.y / dist, wv.z / dist, 0.0f};
 						const float cs_ = dot3(wdir, nn);
 						const float cl = fabsf(wdir.x * e2q.w + wdir.y * e3q.w + wdir.z * e4q.w);
-						if (cs_ > 0.0f && cl > 0.0f) {
-							const float p = random_direction_pdf(cs_);
+						const float ca = dot3(wdir, axis);                 // the lobe's own polar cosine (= cs_ on the diffuse lobe)
+						if (cs_ > 0.0f && cl > 0.0f && ca > 0.0f) {
+							const float p = random_direction_pdf(ca) / accept;
 							const float q = d2 / (cl * m.emit_area);
 							const MaterialDev sm = load_material(sc.materials, mat);
 							const MaterialDev em = load_material(sc.materials, uint32_t(__float_as_int(e1q.w)));
-							const float k = cs_ / TWO_PI_F * p / (p + q);
-							s_c = make_float4(T_before.x * sm.kd.x * em.ka_ks.x * k, T_before.y * sm.kd.y * em.ka_ks.y * k,
-							                  T_before.z * sm.kd.z * em.ka_ks.z * k, __int_as_float(etri));
-							if (s_c.x != 0.0f || s_c.y != 0.0f || s_c.z != 0.0f) {
+							float k = cs_ / TWO_PI_F;
+							f4 refl = sm.kd;
+							if (phong_lobe) {                                // shade.cl:141-143 (ks shares the union slot with ka)
+								refl = sm.ka_ks;
+								k *= powf(ca, sm.Ns);
+							}
+							// X = the value the chain's sample would have had in this direction, then the balance weight
+							const f4 X{T_before.x * refl.x * k * em.ka_ks.x, T_before.y * refl.y * k * em.ka_ks.y, T_before.z * refl.z * k * em.ka_ks.z, 0.0f};
+							const float wb = p / (p + q);
+							s_c = make_float4(X.x * wb, X.y * wb, X.z * wb, __int_as_float(etri));
+							if (m.den && sqrtf(dot4(X, X)) != 0.0f) s_den = wb;
+							if (s_c.x != 0.0f || s_c.y != 0.0f || s_c.z != 0.0f || s_den != 0.0f) {
 								const f4 so = ip + KERNEL_EPSILON * wdir;      // the offset the reference gives its bounce rays (shade.cl:116)
 								s_o = make_float4(so.x, so.y, so.z, 0.0f);
 								s_d = make_float4(wdir.x, wdir.y, wdir.z, __int_as_float(path));
@@ -186,6 +217,7 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 				__stcs(m.sod + pos, s_o);
 				__stcs(m.sdp + pos, s_d);
 				__stcs(m.scon + pos, s_c);
+				if (m.sden) __stcs(m.sden + pos, s_den);
 			}
 		}
 	}
@@ -202,6 +234,7 @@ __global__ void __launch_bounds__(256) k_wave_nee_add(MisDev m, int depth) {
 		float4 r = m.rad[path];
 		r.x += c.x; r.y += c.y; r.z += c.z;
 		m.rad[path] = r;
+		if (m.den) m.den[path] += __ldcs(m.sden + i);
 	}
 }
 

@@ -44,6 +44,27 @@ struct SceneDev {
 	float key_lo[3], key_scale[3];   // sort key of the bounce queues: cell = (origin - key_lo) * key_scale on a 32^3 grid
 };
 
+// ---- checked build (-DMCPT_CHECKED=1, tools/checked_run.sh): every index the walk, the queues and the resolve follow is
+// compared with its bound before use; a violation is counted, its first occurrence recorded (code, value, bound) and
+// the index replaced by a safe one, so the run finishes and mcpt_check_failures() reports it.  compute-sanitizer is
+// closed on this pool; this is the bounds / protocol evidence that stands in for it.  The product build compiles the
+// checks away.
+#ifndef MCPT_CHECKED
+#define MCPT_CHECKED 0
+#endif
+enum { CHK_NODE = 1, CHK_LEAF = 2, CHK_STACK = 3, CHK_HIT = 4, CHK_PERM = 5, CHK_QUEUE = 6, CHK_PATH = 7, CHK_MATERIAL = 8 };
+#if MCPT_CHECKED
+static __device__ unsigned long long g_check[4];      // failures, first code, first value, first bound
+__device__ __forceinline__ bool check_failed(int code, long long value, long long bound) {
+	if (atomicAdd(&g_check[0], 1ull) == 0ull) { g_check[1] = (unsigned long long)code; g_check[2] = (unsigned long long)value; g_check[3] = (unsigned long long)bound; }
+	return true;
+}
+// index in [0, bound) or recorded and replaced by 0
+#define MCPT_CHECK_INDEX(code, idx, bound) do { if ((long long)(idx) < 0 || (long long)(idx) >= (long long)(bound)) { check_failed(code, (long long)(idx), (long long)(bound)); (idx) = 0; } } while (0)
+#else
+#define MCPT_CHECK_INDEX(code, idx, bound) do { } while (0)
+#endif
+
 // 256-bit read-only loads (LDG.E.256, sm_100): a divergent warp costs the L1 one wavefront per lane PER
 // LOAD INSTRUCTION, and this kernel is bound by exactly that, so a 64 B node is two loads instead of four.
 #ifndef MCPT_LDG256
@@ -480,7 +501,11 @@ __device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur ==
 #define MCPT_POP() (--sp, sp < MCPT_SHARED_STACK ? sst_[sp * 128] : w.stack[sp])
 #else
 #define MCPT_STACK_DECL
+#if MCPT_CHECKED
+#define MCPT_PUSH(v) do { if (sp >= STACK_SIZE) { check_failed(CHK_STACK, sp, STACK_SIZE); sp = STACK_SIZE - 1; } w.stack[sp++] = (v); } while (0)
+#else
 #define MCPT_PUSH(v) (w.stack[sp++] = (v))
+#endif
 #define MCPT_POP() (w.stack[--sp])
 #endif
 
@@ -523,6 +548,7 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		const bool hitL = !((tfL < loL) || (tfL < tminlo) || (loL > tprune));
 		const bool hitR = !((tfR < loR) || (tfR < tminlo) || (loR > tprune));
 #else
+		MCPT_CHECK_INDEX(CHK_NODE, cur, sc.ntris - 1);
 		const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
 		float4 a, b, c, lk;
 		ldg256(p, a, b);
@@ -611,7 +637,8 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		int leaf;
 		if (pending != 0) { leaf = pending; pending = 0; }
 		else { leaf = cur; cur = sp > 0 ? MCPT_POP() : WALK_DONE; }
-		const int tri = leaf & 0x7fffffff;
+		int tri = leaf & 0x7fffffff;
+		MCPT_CHECK_INDEX(CHK_LEAF, tri, sc.ntris);
 		const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
 		float4 q0, q1;
 		ldg256(p, q0, q1);
@@ -646,6 +673,9 @@ __device__ __forceinline__ void walk2_resolve(Walk2& w, const SceneDev& sc, cons
 		trace_canonical<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
 	}
 	hit.any = hit.closest >= 0;
+#if MCPT_CHECKED
+	if (hit.closest < -1 || hit.closest >= sc.ntris) { check_failed(CHK_HIT, hit.closest, sc.ntris); hit.closest = -1; hit.any = false; }
+#endif
 }
 
 template <bool COUNT>

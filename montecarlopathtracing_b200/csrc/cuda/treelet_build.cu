@@ -27,6 +27,10 @@
 // an SM's L1 may hold lines another SM's warp has rewritten since.
 #include <cuda_runtime.h>
 
+#ifndef MCPT_CHECKED
+#define MCPT_CHECKED 0
+#endif
+
 #include <cfloat>
 #include <cstdint>
 #include <string>
@@ -328,6 +332,10 @@ __global__ void __launch_bounds__(32 * WARPS) k_treelet(mcpt_bvh_node* nodes, co
 			__threadfence();
 		}
 		prev = __shfl_sync(0xffffffffu, prev, 0);
+#if MCPT_CHECKED
+		// protocol check (checked build): an inner node is reached exactly twice, through in-range parent links
+		if (prev < 0 || prev > 1 || p >= nleaves - 1) { if (lane == 0) atomicExch(status, 7); return; }
+#endif
 		if (prev == 0) return;                       // first arrival only marks the node (:349-352)
 		restructure(nodes, sah, root_area, p, w, lane, status);
 		__syncwarp();
@@ -437,6 +445,21 @@ extern "C" int mcpt_optimize_treelet(int device, const mcpt_bvh_node* nodes_in, 
 	TRY_(cudaMemcpyAsync(nodes_out, nodes.p, sizeof(mcpt_bvh_node) * size_t(nnodes), cudaMemcpyDeviceToHost, st));
 	TRY_(cudaStreamSynchronize(st));
 	TRY_(cudaGetLastError());
+#if MCPT_CHECKED
+	if (h_status == 7) {
+		set_last_error("treelet (checked build): arrival protocol violated (a node reached a third time or a parent link out of range)");
+		return MCPT_ERR_STATE;
+	}
+	if (h_status == 0 && nleaves > 1) {          // every inner node must have been reached exactly twice
+		std::vector<int> h_arrive(size_t(nleaves) - 1);
+		TRY_(cudaMemcpy(h_arrive.data(), arrive.p, sizeof(int) * h_arrive.size(), cudaMemcpyDeviceToHost));
+		for (size_t i = 0; i < h_arrive.size(); ++i)
+			if (h_arrive[i] != 2) {
+				set_last_error("treelet (checked build): inner node " + std::to_string(i) + " was reached " + std::to_string(h_arrive[i]) + " times");
+				return MCPT_ERR_STATE;
+			}
+	}
+#endif
 	if (h_status != 0) {
 		set_last_error("treelet: a subset partition came out empty (non-finite SAH costs); the reference indexes past its slot list here");
 		return MCPT_ERR_STATE;

@@ -1,7 +1,7 @@
 // OBJ/MTL scene loading -> Triangle[] / Material[] / per-triangle material ids.
 //
 // Drop-in for ThirdPartyWrapper::loadObject (thirdpartywrapper.cpp:25-99), which drives
-// tinyobjloader 2.0.0-rc with triangulate=true.  Contract checked by tests/test_host_parity.py
+// tinyobjloader 2.0.0-rc with triangulate=true.  Contract checked by tests/test_host.py
 // against the reference's own code (oracle/_ref): the Triangle and Material arrays are
 // memcmp-equal for the shipped scenes and for fuzzed polygon soups.  What has to match:
 //   * triangle order = face order in the file; polygons are ear-clipped the way tinyobj does

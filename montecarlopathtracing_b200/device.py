@@ -17,7 +17,7 @@ _PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
 TRAVERSAL_REFERENCE, TRAVERSAL_FAST, TRAVERSAL_CANONICAL, TRAVERSAL_WIDE8 = 0, 1, 2, 3
-SAMPLING_REFERENCE, SAMPLING_NEE_MIS = 0, 1
+SAMPLING_REFERENCE, SAMPLING_NEE_MIS, SAMPLING_NEE_MIS_RATIO = 0, 1, 2
 
 EXPORTS = [
     "mcpt_last_error", "mcpt_abi_version", "mcpt_create", "mcpt_destroy", "mcpt_stream", "mcpt_synchronize",
@@ -29,7 +29,7 @@ EXPORTS = [
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
     "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
-    "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived",
+    "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived", "mcpt_phong_accept_table", "mcpt_check_failures",
 ]
 TRACE_NOALLOC_MAX_RAYS = 65536        # MCPT_TRACE_NOALLOC_MAX_RAYS of include/mcpt.h
 
@@ -341,6 +341,22 @@ def derive_scene(triangles, materials, nodes):
         return ctypes.string_at(blob, n.value)
     finally:
         L.mcpt_free_blob(blob)
+
+
+def check_failures(device=0):
+    """Checked build only (MCPT_LIB=build/ab/libmcpt_checked.so): (failures, first code, first value, first bound)."""
+    out = (ctypes.c_uint64 * 4)()
+    if lib().mcpt_check_failures(int(device), out) != 0:
+        raise McptError("mcpt_check_failures: %s" % lib().mcpt_last_error().decode())
+    return tuple(int(x) for x in out)
+
+
+def phong_accept_table():
+    """Acceptance probability of the glossy lobe's rejection loop against angle(mirror direction, normal) (NEE + MIS mode)."""
+    out = np.zeros(1025, np.float32)
+    if lib().mcpt_phong_accept_table(_vp(out), len(out)) != 0:
+        raise McptError("mcpt_phong_accept_table: %s" % lib().mcpt_last_error().decode())
+    return out
 
 
 def build_lbvh(triangles, device=0, return_ms=False):

@@ -1,5 +1,5 @@
 """numpy views of the POD records in include/mcpt_types.h (byte-identical to the reference's
-objdef.h:21-99; sizes asserted below and in tests/test_layout.py)."""
+objdef.h:21-99; sizes asserted below and in tests/test_host.py)."""
 import numpy as np
 
 F4 = (np.float32, (4,))

@@ -1,5 +1,5 @@
-"""BASELINE.json's full-size workload (diningroom stand-in, 1920x1080, depth 16) through properties that do not need
-the CPU oracle at that size (it would take hours): the product walk against the reference-order walk on every
+"""BASELINE.json's full-size workload (diningroom stand-in, 1920x1080, depth 16) through size-independent properties (the
+oracle / reference-kernel comparisons at this size live in tests/test_gpu_headline.py): the product walk against the reference-order walk on every
 primary ray, invariance of the sums under the wave split and under sample sharding, device merge = single render,
 and conservation of the sample count."""
 import numpy as np

@@ -1,4 +1,4 @@
-"""Small invocations of every kernel family for compute-sanitizer (tools/sanitize.sh).  Each target checks its result
+"""Small invocations of every kernel family for the checked build (tools/checked_run.sh; also usable under compute-sanitizer, tools/sanitize.sh, where that tool is open).  Each target checks its result
 against the un-instrumented expectation (host builder / a second run), so a sanitizer pass is also a correctness pass.
 
   treelet   treelet_build.cu: cross-SM arrival counters + __threadfence (the reference's own kernel is racy,
@@ -96,7 +96,12 @@ def main(target, scale):
         assert q["sah"] > 0
     else:
         raise SystemExit("unknown target " + target)
-    print("target %s ok" % target)
+    try:
+        n, code, value, bound = device.check_failures()
+        assert n == 0, "checked build: %d violations, first: code %d value %d bound %d" % (n, code, value, bound)
+        print("target %s ok (checked build: 0 index / protocol violations)" % target)
+    except device.McptError:
+        print("target %s ok" % target)
 
 
 if __name__ == "__main__":
