@@ -16,6 +16,7 @@
 #include "mcpt.h"
 #include "../common/hash128.hpp"
 #include "accel_build.hpp"
+#include "experimental/accel_wide.hpp"
 #include "mcpt_kernels.cuh"
 #include "mcpt_mis.cuh"
 
@@ -1087,32 +1088,17 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	c->host_leaves = dt;
 	c->have_wide = false;
 	CU(cudaStreamSynchronize(c->stream));
-	std::vector<QNode> qn;
-	QFrame qframe{};
-#if MCPT_QNODES
-	const bool have_q = !root_leaf && build_qnodes(fast, qn, qframe);
-#else
-	const bool have_q = false;
-#endif
-#if MCPT_LEAF_LINKS
-	for (DNode& n : fast) {      // after the derived builds, which read the ~triangle form
+	for (DNode& n : fast) {      // leaf links as LEAF_FLAG | triangle: no decode in the walk's loop
 		if (n.left < 0) n.left = int32_t(0x80000000u | uint32_t(~n.left));
 		if (n.right < 0) n.right = int32_t(0x80000000u | uint32_t(~n.right));
 	}
-	for (QNode& n : qn) {
-		if (n.left < 0) n.left = int32_t(0x80000000u | uint32_t(~n.left));
-		if (n.right < 0) n.right = int32_t(0x80000000u | uint32_t(~n.right));
-	}
-#endif
 	const size_t hot_nodes_bytes = (sizeof(DNode) * fast.size() + 255) / 256 * 256;
 	const size_t hot_leaf_bytes = (sizeof(DLeaf) * size_t(ntris) + 255) / 256 * 256;
-	const size_t hot_bytes = hot_nodes_bytes + hot_leaf_bytes + sizeof(QNode) * std::max<size_t>(1, qn.size());
+	const size_t hot_bytes = hot_nodes_bytes + hot_leaf_bytes;
 	CU(c->hot.alloc(hot_bytes));
 	c->fast_nodes = reinterpret_cast<DNode*>(c->hot.p);
 	c->leaves = reinterpret_cast<DLeaf*>(c->hot.p + hot_nodes_bytes);
-	QNode* d_qnodes = reinterpret_cast<QNode*>(c->hot.p + hot_nodes_bytes + hot_leaf_bytes);
 	CU(cudaMemcpyAsync(c->fast_nodes, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
-	if (have_q) CU(cudaMemcpyAsync(d_qnodes, qn.data(), sizeof(QNode) * qn.size(), cudaMemcpyHostToDevice, c->stream));
 	CU(c->nodes_ref.alloc(nnodes));
 	CU(c->tris_ref.alloc(ntris));
 	CU(c->nodes.alloc(dn.size()));
@@ -1129,7 +1115,7 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	float max_abs = 0.0f;
 	for (float v : {nodes[0].bbmin.x, nodes[0].bbmin.y, nodes[0].bbmin.z, nodes[0].bbmax.x, nodes[0].bbmax.y, nodes[0].bbmax.z})
 		max_abs = std::max(max_abs, std::fabs(v));
-	if (!(max_abs < 1e30f) || fast_too_deep || (MCPT_QNODES && !have_q && !root_leaf)) c->force_reference = true;   // no grid frame: degenerate scene
+	if (!(max_abs < 1e30f) || fast_too_deep) c->force_reference = true;
 	// Keep the walk's working set resident in L2: the per-bounce ray / path-state streams (hundreds of MB)
 	// otherwise evict it, and every evicted node costs a whole warp a DRAM round trip (ncu: 20% L2 misses,
 	// 0.6 DRAM node fetches per ray).  Measured on B200: no gain (-1%), so it is opt-in: MCPT_OPT bit 2.
@@ -1151,7 +1137,7 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	c->cache_tris.assign(tris, tris + ntris);
 	c->cache_nodes.assign(nodes, nodes + nnodes);
 	c->geometry_tag = tag;
-	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs, have_q ? d_qnodes : nullptr, qframe};
+	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs};
 	for (int a = 0; a < 3; ++a) {
 		const float lo = a == 0 ? nodes[0].bbmin.x : a == 1 ? nodes[0].bbmin.y : nodes[0].bbmin.z;
 		const float hi = a == 0 ? nodes[0].bbmax.x : a == 1 ? nodes[0].bbmax.y : nodes[0].bbmax.z;

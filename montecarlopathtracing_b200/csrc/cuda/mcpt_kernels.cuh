@@ -13,6 +13,7 @@
 
 #include "mcpt.h"
 #include "mcpt_traverse.cuh"
+#include "experimental/traverse_wide.cuh"   // MCPT_TRAVERSAL_WIDE8 (measured slower; not on the product path)
 
 namespace mcpt {
 
@@ -356,7 +357,7 @@ namespace mcpt {
                                  // more than the pow's 27% of instructions at 2-4 lanes save), so it is off.
 #endif
 #ifndef MCPT_REFILL_THRESHOLD
-#define MCPT_REFILL_THRESHOLD 22
+#define MCPT_REFILL_THRESHOLD 16       // lanes still walking below which a warp refills; with coherence-sorted queues 16 measured +0.6 % over 22 (26: -0.4 %, 30: -0.9 %; profiles/r2l_ab_walk_variants.log)
 #endif
 
 // Job: bool load(unsigned& item, RayRegs&) - false when the item needs no trace (the job has dealt with it); may

@@ -25,6 +25,7 @@
 
 namespace mcpt {
 
+struct WNode;   // experimental/accel_wide.hpp
 struct SceneDev {
 	const mcpt_bvh_node* nodes_ref;
 	const mcpt_triangle* tris_ref;
@@ -39,8 +40,6 @@ struct SceneDev {
 	int root_is_leaf;
 	int opt_flags;               // development switches (MCPT_OPT): bit 1 = one-thread-per-ray kernels instead of persistent ones
 	float max_abs;               // largest |coordinate| of the scene's bounding box (finite-arithmetic guard of the fast walk)
-	const QNode* qnodes;         // 15-bit grid version of fast_nodes (null: not available)
-	QFrame qframe;
 	float key_lo[3], key_scale[3];   // sort key of the bounce queues: cell = (origin - key_lo) * key_scale on a 32^3 grid
 };
 
@@ -70,6 +69,16 @@ __device__ __forceinline__ bool check_failed(int code, long long value, long lon
 #ifndef MCPT_LDG256
 #define MCPT_LDG256 1
 #endif
+// development variants of the cache policy (A/B only): MCPT_LEAF_NOALLOC = leaf / triangle records bypass L1 allocation
+// (each is read once per ray that reaches it), MCPT_NODE_EVICT_LAST = inner nodes are the last lines L1 gives up
+#ifndef MCPT_LEAF_NOALLOC
+#define MCPT_LEAF_NOALLOC 0
+#endif
+#ifndef MCPT_NODE_EVICT_LAST
+#define MCPT_NODE_EVICT_LAST 0
+#endif
+__device__ __forceinline__ void ldg256_leaf(const float4* p, float4& lo, float4& hi);
+__device__ __forceinline__ void ldg256_node(const float4* p, float4& lo, float4& hi);
 __device__ __forceinline__ void ldg256(const float4* p, float4& lo, float4& hi) {
 #if MCPT_LDG256
 	asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -77,6 +86,24 @@ __device__ __forceinline__ void ldg256(const float4* p, float4& lo, float4& hi) 
 	             : "l"(p));
 #else
 	lo = __ldg(p); hi = __ldg(p + 1);
+#endif
+}
+__device__ __forceinline__ void ldg256_leaf(const float4* p, float4& lo, float4& hi) {
+#if MCPT_LEAF_NOALLOC
+	asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+	             : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+	             : "l"(p));
+#else
+	ldg256(p, lo, hi);
+#endif
+}
+__device__ __forceinline__ void ldg256_node(const float4* p, float4& lo, float4& hi) {
+#if MCPT_NODE_EVICT_LAST
+	asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+	             : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+	             : "l"(p));
+#else
+	ldg256(p, lo, hi);
 #endif
 }
 
@@ -286,8 +313,8 @@ __device__ __forceinline__ bool leaf_box_certified(const float4& q0, const float
 __device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restrict__ p, const RayRegs& ray, bool fastok, float tmin,
                                                            float tfar_skip, int& orig_tri) {
 	float4 q2, q3, q4, q5;
-	ldg256(p + 2, q2, q3);
-	ldg256(p + 4, q4, q5);
+	ldg256_leaf(p + 2, q2, q3);
+	ldg256_leaf(p + 4, q4, q5);
 	orig_tri = __float_as_int(q5.w);
 	TriTest out{0.0f, false};
 	const float a1 = ray.direction.x, a2 = ray.direction.y, a3 = ray.direction.z;
@@ -353,18 +380,6 @@ __device__ __forceinline__ TriTest leaf_triangle_certified(const float4* __restr
 constexpr float WINDOW = 2.0e-5f;
 constexpr float BAND = 9.9e-6f;
 constexpr int LEAF_FLAG = int(0x80000000);
-#ifndef MCPT_FUSED_SLAB
-#define MCPT_FUSED_SLAB 1
-#endif
-#ifndef MCPT_QNODES
-#define MCPT_QNODES 0     // 32 B grid-quantised inner nodes: measured SLOWER on B200 (-30% path tracing, -37% coherent rays):
-#endif                    // the PRMT decodes land on the ALU pipe, which min/max and compares already saturate
-#ifndef MCPT_LEAF_LINKS
-#define MCPT_LEAF_LINKS 1 // fast nodes store leaf links as LEAF_FLAG | triangle (no decode in the loop)
-#endif
-#ifndef MCPT_POSTPONE_LEAF
-#define MCPT_POSTPONE_LEAF 0   // 1: keep descending after the first leaf (Aila-Laine "postponed leaf"): measured -1.7% on the loop, -6% coherent
-#endif
 
 struct CandList {
 	float t0, t1, t2;
@@ -419,15 +434,11 @@ __device__ __forceinline__ bool cand_resolve(const CandList& c, float best, HitR
 // (a "round" = descend inner nodes until a leaf turns up, then test the leaves at hand).
 struct Walk2 {
 	int stack[STACK_SIZE];     // >= 0 inner node; LEAF_FLAG | triangle for a leaf
-	int sp, cur, pending;      // pending: postponed leaf (0 = none; leaf codes carry LEAF_FLAG, so they are never 0)
+	int top;                   // MCPT_TOP_CACHE: newest stack entry (0 = none)
+	int sp, cur;
 	float best;
 	float rx, ry, rz;
-#if MCPT_FUSED_SLAB
 	float c1x, c1y, c1z, c2x, c2y, c2z;   // plane distance = fma(plane, r, c): c1 for bmin planes, c2 for bmax planes
-#endif
-#if MCPT_QNODES
-	float qax, qay, qaz, qbx, qby, qbz;   // plane distance = fma(2^15 + q, qb, qa)
-#endif
 	CandList cl;
 	bool fastok, slow;         // slow: zero direction component or single-triangle scene -> reference walk
 	unsigned ln, lt, lr;       // instrumentation
@@ -438,7 +449,6 @@ __device__ __forceinline__ void walk2_init(Walk2& w, const SceneDev& sc, const R
 	w.slow = ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf;
 	w.rx = 1.0f / ray.direction.x; w.ry = 1.0f / ray.direction.y; w.rz = 1.0f / ray.direction.z;
 	w.fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
-#if MCPT_FUSED_SLAB
 	{
 		// -o*r with the rounding error of the fused form (<= 2.1 * 2^-24 |o*r| per plane, see walk2_round) folded
 		// in: bmin planes are the near ones when r > 0, so c1 moves them down and c2 moves the bmax planes up by
@@ -455,35 +465,16 @@ __device__ __forceinline__ void walk2_init(Walk2& w, const SceneDev& sc, const R
 		                  sc.max_abs * fmaxf(fmaxf(fabsf(w.rx), fabsf(w.ry)), fabsf(w.rz));
 		w.slow = w.slow || !w.fastok || !(big < 1e37f);
 	}
-#endif
-#if MCPT_QNODES
-	{
-		// Grid plane q of axis a lies at lo + q * step, so its distance is q * (step / d) + (lo - o) / d.  q arrives
-		// as the float M = 2^15 + q (one PRMT, see walk2_round), hence qa = (lo - o) / d - 2^15 qb.
-		// Error budget, in units of |step / d| (e = 2^-24, k = |lo - o| / scene extent, grid = 2^15 steps per extent):
-		//   qb, q * qb: 2e q <= 2^-8;  (lo - o) * r: 3e * 2^15 k;  qa's subtraction and the final fma: 2 * e * 2^15 (k + 1);
-		//   the reference's own fl(fl(p - o) / d) on the true plane: 2e * 2^15 (k + 1).
-		// For k <= 32 that is < 0.45 steps in total; the builder rounds outwards and adds QNODE_MARGIN = 2 steps, so a box
-		// the reference's test accepts is always accepted here.  Rays farther than 32 extents from the frame, or whose
-		// arithmetic could overflow, take the reference walk.
-		const float ux = sc.qframe.lo[0] - ray.origin.x, uy = sc.qframe.lo[1] - ray.origin.y, uz = sc.qframe.lo[2] - ray.origin.z;
-		w.qbx = sc.qframe.step[0] * w.rx; w.qby = sc.qframe.step[1] * w.ry; w.qbz = sc.qframe.step[2] * w.rz;
-		w.qax = ux * w.rx - 32768.0f * w.qbx; w.qay = uy * w.ry - 32768.0f * w.qby; w.qaz = uz * w.rz - 32768.0f * w.qbz;
-		const float far = fmaxf(fmaxf(fabsf(ux), fabsf(uy)), fabsf(uz));
-		const float big = (far + 2.0f * sc.qframe.extent) * fmaxf(fmaxf(fabsf(w.rx), fabsf(w.ry)), fabsf(w.rz));
-		w.slow = w.slow || !w.fastok || !(far <= 32.0f * sc.qframe.extent) || !(big < 1e37f);
-	}
-#endif
 	w.sp = 0;
+	w.top = 0;
 	w.cur = w.slow ? WALK_DONE : 0;
-	w.pending = 0;
 	w.best = FLT_MAX;
 	w.cl.n = 0; w.cl.overflow = false;
 	w.cl.t0 = w.cl.t1 = w.cl.t2 = 0.f; w.cl.tri0 = w.cl.tri1 = w.cl.tri2 = 0; w.cl.rank0 = w.cl.rank1 = w.cl.rank2 = 0;
 	w.ln = w.lt = w.lr = 0;
 }
 
-__device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur == WALK_DONE && w.pending == 0; }
+__device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur == WALK_DONE; }
 
 // The walk's stack lives in local memory: every push / pop is an LSU access whose lines also compete for L1 and,
 // written through, for L2 (ncu r1n: 26% of the kernel's L1 wavefronts, 16% of its L2 requests).  MCPT_SHARED_STACK
@@ -492,8 +483,8 @@ __device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur ==
 #ifndef MCPT_SHARED_STACK
 #define MCPT_SHARED_STACK 0
 #endif
-#ifndef MCPT_SELECT_PREDICATED
-#define MCPT_SELECT_PREDICATED 1
+#ifndef MCPT_TOP_CACHE
+#define MCPT_TOP_CACHE 0
 #endif
 #if MCPT_SHARED_STACK
 #define MCPT_STACK_DECL __shared__ int sstack_[MCPT_SHARED_STACK * 128]; int* const sst_ = sstack_ + threadIdx.x;
@@ -502,62 +493,49 @@ __device__ __forceinline__ bool walk2_finished(const Walk2& w) { return w.cur ==
 #else
 #define MCPT_STACK_DECL
 #if MCPT_CHECKED
-#define MCPT_PUSH(v) do { if (sp >= STACK_SIZE) { check_failed(CHK_STACK, sp, STACK_SIZE); sp = STACK_SIZE - 1; } w.stack[sp++] = (v); } while (0)
+#define MCPT_STORE_(v) do { if (sp >= STACK_SIZE) { check_failed(CHK_STACK, sp, STACK_SIZE); sp = STACK_SIZE - 1; } w.stack[sp++] = (v); } while (0)
 #else
-#define MCPT_PUSH(v) (w.stack[sp++] = (v))
+#define MCPT_STORE_(v) (w.stack[sp++] = (v))
 #endif
+#if MCPT_TOP_CACHE
+// the newest entry stays in a register (0 = none: the root is never pushed and leaf codes carry LEAF_FLAG): a push that
+// finds the register free and the pop that follows it touch no memory at all - the pattern of every "near child is a
+// leaf, far child waits" visit
+#define MCPT_PUSH(v) do { if (top != 0) MCPT_STORE_(top); top = (v); } while (0)
+#define MCPT_POP() (top != 0 ? take_top_(top) : w.stack[--sp])
+#define MCPT_NONEMPTY ((top | sp) != 0)
+#else
+#define MCPT_PUSH(v) MCPT_STORE_(v)
 #define MCPT_POP() (w.stack[--sp])
 #endif
+#endif
+#ifndef MCPT_NONEMPTY
+#define MCPT_NONEMPTY (sp > 0)
+#endif
+__device__ __forceinline__ int take_top_(int& top) { const int t = top; top = 0; return t; }
 
 template <bool COUNT>
 __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const RayRegs& ray, float tmin) {
 	MCPT_STACK_DECL
 	const float rx = w.rx, ry = w.ry, rz = w.rz;
-	int cur = w.cur, sp = w.sp, pending = w.pending;
-	float best = w.best;
-#if MCPT_FUSED_SLAB || MCPT_QNODES
-	const float tminlo = tmin * (1.0f - 0x1p-19f);
+	int cur = w.cur, sp = w.sp;
+#if MCPT_TOP_CACHE
+	int top = w.top;
 #endif
+	float best = w.best;
+	const float tminlo = tmin * (1.0f - 0x1p-19f);
 	// per-ray constants are copied out of `w` (which lives in local memory because of its stack array): read
 	// through `w` inside the loop they would be reloaded after every stack store
-#if MCPT_QNODES
-	const float qax = w.qax, qay = w.qay, qaz = w.qaz, qbx = w.qbx, qby = w.qby, qbz = w.qbz;
-	const unsigned snx = qbx < 0.0f ? 0x7324u : 0x7104u, sny = qby < 0.0f ? 0x7324u : 0x7104u, snz = qbz < 0.0f ? 0x7324u : 0x7104u;
-	const unsigned sfx = snx ^ 0x0220u, sfy = sny ^ 0x0220u, sfz = snz ^ 0x0220u;
-#elif MCPT_FUSED_SLAB
 	const float c1x = w.c1x, c1y = w.c1y, c1z = w.c1z, c2x = w.c2x, c2y = w.c2y, c2z = w.c2z;
-#endif
 	// ---- inner nodes: conservative tests of both children, near child first
 	while (cur >= 0 && cur != WALK_DONE) {
-#if MCPT_QNODES
-		float4 qa_, qb_;
-		ldg256(reinterpret_cast<const float4*>(sc.qnodes + cur), qa_, qb_);
-		const int2 link = make_int2(__float_as_int(qb_.z), __float_as_int(qb_.w));
-		if (COUNT) ++w.ln;
-		const float tprune = __fmaf_rn(best, PRUNE_REL, PRUNE_ABS);
-		// 2^15 + q as a float: the two bytes of q land in mantissa bits 8..22 under the exponent byte 0x47.  The same
-		// PRMT picks the NEAR or the FAR plane of the axis (low half = min plane, high half = max plane; which one is
-		// near depends only on the sign of the ray direction), so no min/max per axis is needed.
-		#define QSEL(word, sel) __uint_as_float(__byte_perm(__float_as_uint(word), 0x47000000u, sel))
-		const float loL = fmaxf(fmaxf(__fmaf_rn(QSEL(qa_.x, snx), qbx, qax), __fmaf_rn(QSEL(qa_.y, sny), qby, qay)), __fmaf_rn(QSEL(qa_.z, snz), qbz, qaz));
-		const float tfL = fminf(fminf(__fmaf_rn(QSEL(qa_.x, sfx), qbx, qax), __fmaf_rn(QSEL(qa_.y, sfy), qby, qay)), __fmaf_rn(QSEL(qa_.z, sfz), qbz, qaz));
-		const float loR = fmaxf(fmaxf(__fmaf_rn(QSEL(qa_.w, snx), qbx, qax), __fmaf_rn(QSEL(qb_.x, sny), qby, qay)), __fmaf_rn(QSEL(qb_.y, snz), qbz, qaz));
-		const float tfR = fminf(fminf(__fmaf_rn(QSEL(qa_.w, sfx), qbx, qax), __fmaf_rn(QSEL(qb_.x, sfy), qby, qay)), __fmaf_rn(QSEL(qb_.y, sfz), qbz, qaz));
-		#undef QSEL
-		// all evaluation error is inside the builder's outward margin (walk2_init); tmin only needs its own ulp
-		const bool hitL = !((tfL < loL) || (tfL < tminlo) || (loL > tprune));
-		const bool hitR = !((tfR < loR) || (tfR < tminlo) || (loR > tprune));
-#else
 		MCPT_CHECK_INDEX(CHK_NODE, cur, sc.ntris - 1);
 		const float4* p = reinterpret_cast<const float4*>(sc.fast_nodes + cur);
 		float4 a, b, c, lk;
-		ldg256(p, a, b);
-		ldg256(p + 2, c, lk);
+		ldg256_node(p, a, b);
+		ldg256_node(p + 2, c, lk);
 		const int2 link = make_int2(__float_as_int(lk.x), __float_as_int(lk.y));
 		if (COUNT) ++w.ln;
-#endif
-#if MCPT_QNODES
-#elif MCPT_FUSED_SLAB
 		// plane distance as ONE fma(plane, 1/d, -o/d -+ S).  Against the reference's fl(fl(plane - o) / d) = T:
 		// |t - T| <= 4.1 * 2^-24 |T| + 2.1 * 2^-24 |o/d|; the second (absolute) part is already inside c1/c2, the
 		// relative part is the 2^-20 max(|tn|, |tf|) below.  The tmin and pruning tests take their relative slack
@@ -576,34 +554,7 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 		const float loR = __fmaf_rn(fmaxf(fabsf(tnR), fabsf(tfR)), -SLAB_SLACK, tnR);
 		const bool hitL = !((tfL < loL) || (tfL < tminlo) || (tnL > tprune));
 		const bool hitR = !((tfR < loR) || (tfR < tminlo) || (tnR > tprune));
-#else
-		const float tprune = best * PRUNE_REL + PRUNE_ABS;
-		// (bb - o) * (1/d): |computed - reference| <= 2^-22 |t|, covered 4x by the 2^-20 relative slack.  (A single
-		// fused bb*(1/d) - o*(1/d) is cheaper but its error scales with |o/d|: rays nearly parallel to an axis
-		// would then accept every box - measured 3x slower on random rays, so it is not used.)
-		float o1, o2, n0, n1, n2, f0, f1, f2;
-		o1 = (a.x - ray.origin.x) * rx; o2 = (a.w - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
-		o1 = (a.y - ray.origin.y) * ry; o2 = (b.x - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
-		o1 = (a.z - ray.origin.z) * rz; o2 = (b.y - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
-		float tnL = fmaxf(fmaxf(n0, n1), n2), tfL = fminf(fminf(f0, f1), f2);
-		o1 = (b.z - ray.origin.x) * rx; o2 = (c.y - ray.origin.x) * rx; n0 = fminf(o1, o2); f0 = fmaxf(o1, o2);
-		o1 = (b.w - ray.origin.y) * ry; o2 = (c.z - ray.origin.y) * ry; n1 = fminf(o1, o2); f1 = fmaxf(o1, o2);
-		o1 = (c.x - ray.origin.z) * rz; o2 = (c.w - ray.origin.z) * rz; n2 = fminf(o1, o2); f2 = fmaxf(o1, o2);
-		float tnR = fmaxf(fmaxf(n0, n1), n2), tfR = fminf(fminf(f0, f1), f2);
-		const float sL = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnL), fabsf(tfL)), tmin);
-		const float sR = SLAB_SLACK * fmaxf(fmaxf(fabsf(tnR), fabsf(tfR)), tmin);
-		const float loL = tnL - sL, loR = tnR - sR;
-		// comparisons are false on NaN => not rejected (conservative)
-		const bool hitL = !((tfL < loL) || (tfL < tmin - sL) || (loL > tprune));
-		const bool hitR = !((tfR < loR) || (tfR < tmin - sR) || (loR > tprune));
-#endif
-#if MCPT_LEAF_LINKS
 		const int cl_ = link.x, cr_ = link.y;
-#else
-		int cl_ = link.x < 0 ? (LEAF_FLAG | ~link.x) : link.x;
-		int cr_ = link.y < 0 ? (LEAF_FLAG | ~link.y) : link.y;
-#endif
-#if MCPT_SELECT_PREDICATED
 		// one straight-line selection instead of four divergent arms (ncu r1n: the arms ran at 11 of 32 lanes)
 		{
 			const bool swap = loR < loL, both = hitL && hitR;
@@ -612,36 +563,20 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 			int nxt = nearc;
 			if (!(hitL || hitR)) {
 				nxt = WALK_DONE;
-				if (sp > 0) nxt = MCPT_POP();
+				if (MCPT_NONEMPTY) nxt = MCPT_POP();
 			}
 			cur = nxt;
 		}
-#else
-		if (hitL && hitR) {
-			const bool swap = loR < loL;
-			const int nearc = swap ? cr_ : cl_, farc = swap ? cl_ : cr_;
-			MCPT_PUSH(farc);           // cannot overflow: mcpt_upload_scene checks the depth of the fast tree against STACK_SIZE
-			cur = nearc;
-		} else if (hitL) cur = cl_;
-		else if (hitR) cur = cr_;
-		else cur = sp > 0 ? MCPT_POP() : WALK_DONE;
-#endif
-#if MCPT_POSTPONE_LEAF
-		// the first leaf found is postponed so that the lane keeps traversing while its warp mates still
-		// search: candidates need not arrive in any particular order (see the replay argument above)
-		if (cur < 0 && pending == 0) { pending = cur; cur = sp > 0 ? MCPT_POP() : WALK_DONE; }
-#endif
 	}
 	// ---- leaves: certified reference box test, then the certified triangle test
-	while (pending != 0 || cur < 0) {
-		int leaf;
-		if (pending != 0) { leaf = pending; pending = 0; }
-		else { leaf = cur; cur = sp > 0 ? MCPT_POP() : WALK_DONE; }
+	while (cur < 0) {
+		const int leaf = cur;
+		cur = MCPT_NONEMPTY ? MCPT_POP() : WALK_DONE;
 		int tri = leaf & 0x7fffffff;
 		MCPT_CHECK_INDEX(CHK_LEAF, tri, sc.ntris);
 		const float4* p = reinterpret_cast<const float4*>(sc.leaves + tri);
 		float4 q0, q1;
-		ldg256(p, q0, q1);
+		ldg256_leaf(p, q0, q1);
 		if (COUNT) ++w.lr;
 		if (leaf_box_certified(q0, q1, ray, rx, ry, rz, w.fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
 			if (COUNT) ++w.lt;
@@ -653,7 +588,10 @@ __device__ __forceinline__ void walk2_round(Walk2& w, const SceneDev& sc, const 
 			}
 		}
 	}
-	w.cur = cur; w.sp = sp; w.pending = pending; w.best = best;
+	w.cur = cur; w.sp = sp; w.best = best;
+#if MCPT_TOP_CACHE
+	w.top = top;
+#endif
 }
 
 // The reference's (t, triangle) from the finished walk; rays the fast walk cannot decide are re-traced.
@@ -685,127 +623,6 @@ __device__ __forceinline__ void trace_ordered2(const SceneDev& sc, const RayRegs
 	walk2_init(w, sc, ray);
 	while (!walk2_finished(w)) walk2_round<COUNT>(w, sc, ray, tmin);
 	walk2_resolve<COUNT>(w, sc, ray, tmin, hit, cnt_nodes, cnt_tris);
-}
-
-// ------------------------------------------------------------------ 8-wide compressed traversal (experimental)
-// Same candidate / replay logic as trace_ordered2; inner tests run on 8-bit quantised child boxes that
-// contain the true child boxes (outward rounding, verified in exact arithmetic at build time).  Plane
-// distances are one FFMA each: t = q * (scale/d) + (p - o)/d.  With A = (p-o)*r, B = scale*r the computed
-// value is within 2^-22 (|A| + 255 |B|) of the exact distance to the quantised plane; every near plane is
-// moved down and every far plane up by s = 2^-20 (|A| + 256 |B|) PER AXIS (a per-axis slack cannot blow
-// up the way a per-ray |o/d| term would: an axis the ray is parallel to has huge planes AND a huge slack,
-// but they only matter when the origin is within 1e-6 of that slab's boundary).
-constexpr int WSTACK = 32;
-
-template <bool COUNT>
-__device__ __forceinline__ void trace_wide(const SceneDev& sc, const RayRegs& ray, float tmin, HitRegs& hit,
-                                           unsigned long long* cnt_nodes, unsigned long long* cnt_tris) {
-	if (ray.direction.x == 0.0f || ray.direction.y == 0.0f || ray.direction.z == 0.0f || sc.root_is_leaf) {
-		trace_reference<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
-		return;
-	}
-	// 2^23 * scale / d must stay finite for the byte -> float trick below: steeper rays use the binary walk
-	if (!(fabsf(ray.direction.x) > 1e-20f && fabsf(ray.direction.y) > 1e-20f && fabsf(ray.direction.z) > 1e-20f)) {
-		trace_ordered2<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
-		return;
-	}
-	const float rx = 1.0f / ray.direction.x, ry = 1.0f / ray.direction.y, rz = 1.0f / ray.direction.z;
-	const bool fastok = fabsf(ray.direction.x) > 1e-30f && fabsf(ray.direction.y) > 1e-30f && fabsf(ray.direction.z) > 1e-30f;
-	const bool posx = ray.direction.x >= 0.0f, posy = ray.direction.y >= 0.0f, posz = ray.direction.z >= 0.0f;
-	const unsigned octinv = (posx ? 1u : 0u) | (posy ? 2u : 0u) | (posz ? 4u : 0u);
-	uint2 stack[WSTACK];
-	int sp = 0;
-	uint2 ng = make_uint2(0u, 0x80000000u);       // virtual group holding the root (imask 0 => relative index 0)
-	float best = FLT_MAX;
-	CandList cl;
-	cl.n = 0; cl.overflow = false;
-	cl.t0 = cl.t1 = cl.t2 = 0.f; cl.tri0 = cl.tri1 = cl.tri2 = 0; cl.rank0 = cl.rank1 = cl.rank2 = 0;
-	bool any = false;
-	unsigned ln = 0, lt = 0, lr = 0;
-	for (;;) {
-		uint2 tg = make_uint2(0u, 0u);
-		if (ng.y > 0x00FFFFFFu) {
-			// ---- next inner child of the current group (highest bit first = nearest octant first)
-			const unsigned bit = 31u - unsigned(__clz(int(ng.y)));
-			const unsigned gmask = ng.y & 0xFFu;
-			ng.y &= ~(1u << bit);
-			if (ng.y > 0x00FFFFFFu) { if (sp < WSTACK) stack[sp++] = ng; else cl.overflow = true; }
-			const unsigned slot = (bit - 24u) ^ octinv;
-			const unsigned rel = unsigned(__popc(gmask & ((1u << slot) - 1u)));
-			const float4* p = reinterpret_cast<const float4*>(sc.wnodes + (ng.x + rel));
-			const float4 n0 = __ldg(p), n1 = __ldg(p + 1), n2 = __ldg(p + 2), n3 = __ldg(p + 3), n4 = __ldg(p + 4);
-			if (COUNT) ++ln;
-			const unsigned ew = __float_as_uint(n0.w);
-			const float sx = __uint_as_float((ew & 0xFFu) << 23), sy = __uint_as_float(((ew >> 8) & 0xFFu) << 23),
-			            sz = __uint_as_float(((ew >> 16) & 0xFFu) << 23);
-			const float Bx = sx * rx, By = sy * ry, Bz = sz * rz;
-			const float Ax = (n0.x - ray.origin.x) * rx, Ay = (n0.y - ray.origin.y) * ry, Az = (n0.z - ray.origin.z) * rz;
-			// A byte q becomes the float 2^23 + q with ONE permute (0x4B0000qq); the 2^23 * B is folded into the
-			// constant term, whose rounding costs at most half a quantisation step |B|/2 -> one extra |B| of slack.
-			const float slx = SLAB_SLACK * (fabsf(Ax) + 256.0f * fabsf(Bx)) + fabsf(Bx), sly = SLAB_SLACK * (fabsf(Ay) + 256.0f * fabsf(By)) + fabsf(By),
-			            slz = SLAB_SLACK * (fabsf(Az) + 256.0f * fabsf(Bz)) + fabsf(Bz);
-			const float Mx = Ax - 8388608.0f * Bx, My = Ay - 8388608.0f * By, Mz = Az - 8388608.0f * Bz;
-			const float Anx = Mx - slx, Afx = Mx + slx, Any = My - sly, Afy = My + sly, Anz = Mz - slz, Afz = Mz + slz;
-			// near / far quantised planes per axis, chosen by the ray octant
-			const unsigned qlx0 = __float_as_uint(n2.x), qlx1 = __float_as_uint(n2.y), qly0 = __float_as_uint(n2.z), qly1 = __float_as_uint(n2.w);
-			const unsigned qlz0 = __float_as_uint(n3.x), qlz1 = __float_as_uint(n3.y), qhx0 = __float_as_uint(n3.z), qhx1 = __float_as_uint(n3.w);
-			const unsigned qhy0 = __float_as_uint(n4.x), qhy1 = __float_as_uint(n4.y), qhz0 = __float_as_uint(n4.z), qhz1 = __float_as_uint(n4.w);
-			const unsigned nx[2] = {posx ? qlx0 : qhx0, posx ? qlx1 : qhx1}, fx[2] = {posx ? qhx0 : qlx0, posx ? qhx1 : qlx1};
-			const unsigned ny[2] = {posy ? qly0 : qhy0, posy ? qly1 : qhy1}, fy[2] = {posy ? qhy0 : qly0, posy ? qhy1 : qly1};
-			const unsigned nz[2] = {posz ? qlz0 : qhz0, posz ? qlz1 : qhz1}, fz[2] = {posz ? qhz0 : qlz0, posz ? qhz1 : qlz1};
-			const unsigned meta[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
-			const float tprune = best * PRUNE_REL + PRUNE_ABS;
-			unsigned hitmask = 0u;
-#pragma unroll
-			for (int c = 0; c < 8; ++c) {
-				const int w = c >> 2, sh = (c & 3) * 8;
-				const float tnx = __fmaf_rn(__uint_as_float(__byte_perm(nx[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bx, Anx);
-				const float tny = __fmaf_rn(__uint_as_float(__byte_perm(ny[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), By, Any);
-				const float tnz = __fmaf_rn(__uint_as_float(__byte_perm(nz[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bz, Anz);
-				const float tfx = __fmaf_rn(__uint_as_float(__byte_perm(fx[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bx, Afx);
-				const float tfy = __fmaf_rn(__uint_as_float(__byte_perm(fy[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), By, Afy);
-				const float tfz = __fmaf_rn(__uint_as_float(__byte_perm(fz[w], 0x4B000000u, 0x7440u | unsigned(c & 3))), Bz, Afz);
-				const float tn = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, tmin));
-				const float tf = fminf(fminf(tfx, tfy), fminf(tfz, tprune));
-				const unsigned m = (meta[w] >> sh) & 0xFFu;
-				if (!(tn > tf)) {                           // false on NaN => kept (conservative)
-					unsigned idx = m & 31u;
-					if (idx >= 24u) idx ^= octinv;
-					hitmask |= (m >> 5) << idx;
-				}
-			}
-			ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xFF000000u) | (ew >> 24));
-			tg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00FFFFFFu);
-		}
-		// ---- leaf records of this node: exact reference box test, then the exact triangle test
-		while (tg.y != 0u) {
-			const unsigned bit = unsigned(__ffs(int(tg.y))) - 1u;
-			tg.y &= tg.y - 1u;
-			const float4* p = reinterpret_cast<const float4*>(sc.wleaves + (tg.x + bit));
-			const float4 q0 = __ldg(p), q1 = __ldg(p + 1);
-			if (COUNT) ++lr;
-			if (leaf_box_certified(q0, q1, ray, rx, ry, rz, fastok, tmin, best * PRUNE_REL + PRUNE_ABS)) {
-				if (COUNT) ++lt;
-				int orig;
-				TriTest r = leaf_triangle_certified(p, ray, fastok, tmin, best + 2.0f * WINDOW, orig);
-				if (r.valid) {
-					any = true;
-					if (r.t < best) best = r.t;
-					if (!(r.t - best > WINDOW)) cand_insert(cl, best, r.t, orig, __float_as_int(q0.w));
-				}
-			}
-		}
-		if (ng.y <= 0x00FFFFFFu) {
-			if (sp == 0) break;
-			ng = stack[--sp];
-		}
-	}
-	if (COUNT) { atomicAdd(cnt_nodes, (unsigned long long)ln); atomicAdd(cnt_tris, (unsigned long long)lt); atomicAdd(cnt_nodes + 5, (unsigned long long)lr); }
-	hit.any = any;
-	if (cl.overflow || !cand_resolve(cl, best, hit)) {
-		hit = HitRegs{FLT_MAX, -1, 0, false};
-		trace_canonical<COUNT>(sc, ray, tmin, hit, cnt_nodes, cnt_tris);
-	}
 }
 
 }  // namespace mcpt
