@@ -51,6 +51,36 @@ __device__ __forceinline__ f4 operator/(f4 a, float s) {
 	return {a.x / s, a.y / s, a.z / s, a.w / s};
 #endif
 }
+// Division of a path's throughput by 2 pi (shade.cl:120,143).  Throughputs shrink by ~2^-7 per bounce and the Phong
+// lobe's pow(cos, Ns = 4000) adds factors of 2^-100 at once: on the diningroom stand-in 5 % of the live rays carry a
+// channel below 2^-120 at bounce 8 and 13 % a denormal one at bounce 14 (tools/throughput_probe.py).  There the
+// hardware's division takes its slow path - a ~100-instruction subroutine the whole warp waits for while one or two
+// lanes run it: 22 % of k_wave_shade's warp instructions at a mid-depth bounce (ncu r2m).  Both detours below return
+// the correctly rounded float quotient, i.e. the same bits as `a / b`:
+//  * 2^-120 <= |a| < 2^-40: ((a * 2^64) / b) * 2^-64.  Scaling by a power of two commutes with round-to-nearest while
+//    nothing leaves the normal range (|a / b| >= 2^-123 for b = 2 pi, so the last product is exact).
+//  * 0 < |a| < 2^-120 (quotient possibly denormal): float(double(a) / double(b)).  A quotient of two 24-bit numbers that
+//    is not itself a rounding midpoint of the (at most 24-bit) target lies at least 2^-49 (relative) away from every
+//    midpoint, the 53-bit division moves it by at most 2^-53, so the second rounding decides as a single one would; the
+//    conversion rounds into the denormal range correctly (-ftz=false).
+#ifndef MCPT_SCALED_DIV
+#define MCPT_SCALED_DIV 1       // bit 0: power-of-two scaling (+0.4 % on the headline loop); bit 1: double-precision detour for the
+                                // smallest operands (bit-exact too, but -0.9 %: the extra branch costs more than the subroutine it avoids; off)
+#endif
+__device__ __forceinline__ float fdiv_two_pi(float a) {
+	const float aa = fabsf(a);
+#if MCPT_SCALED_DIV & 2
+	if (aa < 0x1p-120f && aa > 0.0f) return float(double(a) / double(TWO_PI_F));
+#endif
+#if MCPT_SCALED_DIV & 1
+	const bool tiny = aa < 0x1p-40f && aa >= 0x1p-120f;
+	const float up = tiny ? 0x1p64f : 1.0f, down = tiny ? 0x1p-64f : 1.0f;
+	return fdiv(a * up, TWO_PI_F) * down;
+#else
+	return fdiv(a, TWO_PI_F);
+#endif
+}
+__device__ __forceinline__ f4 div_two_pi(f4 a) { return {fdiv_two_pi(a.x), fdiv_two_pi(a.y), fdiv_two_pi(a.z), fdiv_two_pi(a.w)}; }
 __device__ __forceinline__ f4 operator-(f4 a) { return {-a.x, -a.y, -a.z, -a.w}; }
 __device__ __forceinline__ float dot3(f4 a, f4 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ float dot4(f4 a, f4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
@@ -228,7 +258,7 @@ __device__ __forceinline__ MaterialDev load_material(const mcpt_material* __rest
 // factor open: colour holds colour * ks, the arguments and the trailing factor go to *defer, and the caller finishes
 // with finish_phong() once it has evaluated the pows of a whole block in dense warps.  Same operations, same order.
 struct PhongDefer { float x, y, post; bool pending; };
-__device__ __forceinline__ void finish_phong(f4& color, float p, float post) { color = color * p * post / TWO_PI_F; }
+__device__ __forceinline__ void finish_phong(f4& color, float p, float post) { color = div_two_pi(color * p * post); }
 
 __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
                                           RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
@@ -264,8 +294,8 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		if (specular && defer) {
 			color = color * mat.ka_ks;
 			defer->x = dot3(new_dir, axis); defer->y = mat.Ns; defer->post = dot3(new_dir, n); defer->pending = true;
-		} else if (specular) color = color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n) / TWO_PI_F;
-		else color = color * mat.kd * dot3(new_dir, n) / TWO_PI_F;
+		} else if (specular) color = div_two_pi(color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n));
+		else color = div_two_pi(color * mat.kd * dot3(new_dir, n));
 		if (diffuse_lobe) *diffuse_lobe = !specular;
 		if (phong_axis && specular) *phong_axis = f4{axis.x, axis.y, axis.z, 1.0f};
 		seed_slot = seed;
