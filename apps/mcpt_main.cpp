@@ -27,6 +27,7 @@
 #include <thread>
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include <vector>
 
 #include <sys/mman.h>
@@ -51,6 +52,8 @@ struct State {
 	bool use_cache = true;       // --no-cache
 	const char* cache_state = "off";
 	double load_s = 0.0;         // OBJ/MTL (or cache) -> triangles, materials, nodes, layout blob
+	mutable double create_s = 0.0, upload_s = 0.0;   // slowest device: mcpt_create (first CUDA call of its thread / process), scene upload
+	mutable std::mutex timing_mutex;
 	std::vector<mcpt_ctx*> ctx;
 	int spp = 0;             // config "attempt"
 	uint32_t run_seed = 1;
@@ -109,12 +112,20 @@ mcpt_ctx* make_context(const State& s, int g, int ngpus) {
 	p.sampling = s.mis ? (s.mis_ratio ? MCPT_SAMPLING_NEE_MIS_RATIO : MCPT_SAMPLING_NEE_MIS) : MCPT_SAMPLING_REFERENCE;
 	p.run_seed = s.run_seed;
 	p.traversal = MCPT_TRAVERSAL_FAST;
+	auto t0 = std::chrono::steady_clock::now();
 	mcpt_ctx* c = mcpt_create(&p);
 	if (!c) die("mcpt_create", mcpt_last_error());
+	auto t1 = std::chrono::steady_clock::now();
 	int rc = s.derived ? mcpt_upload_scene_derived(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()),
 	                                                s.derived, s.derived_bytes, 0)
 	                   : mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
 	if (rc || mcpt_set_camera(c, &s.cfg.camera)) die("scene upload", mcpt_last_error());
+	auto t2 = std::chrono::steady_clock::now();
+	{
+		std::lock_guard<std::mutex> lock(s.timing_mutex);
+		s.create_s = std::max(s.create_s, std::chrono::duration<double>(t1 - t0).count());
+		s.upload_s = std::max(s.upload_s, std::chrono::duration<double>(t2 - t1).count());
+	}
 	return c;
 }
 
@@ -282,10 +293,17 @@ void run_overlapped(State& s, int frames, int batch, std::chrono::steady_clock::
 }
 
 // ---- --procs N: one process per device
+std::vector<pid_t> g_unreaped;       // workers whose results are in but whose processes are still exiting
+void reap_workers() {
+	for (pid_t p : g_unreaped) { int st = 0; waitpid(p, &st, 0); }
+	g_unreaped.clear();
+}
+struct WorkerShared { int turn; int next_block; };   // --overlap-init: whose turn it is to initialise CUDA; next unrendered frame
 struct WorkerResult {
 	int ok;
 	uint64_t rays, paths;
 	double ready_s, done_s;      // since t0 (CLOCK_MONOTONIC is shared by the processes of a box)
+	double create_s, upload_s;   // mcpt_create (the process's first CUDA call), scene upload
 	char error[200];
 };
 
@@ -312,11 +330,14 @@ void run_processes(State& s, int procs, int frames, std::chrono::steady_clock::t
                    mcpt_stats& tot, double& all_ready_s, double& first_ready_s, double& render_done_s) {
 	const size_t npix = size_t(s.cfg.width) * size_t(s.cfg.height);
 	const size_t plane_bytes = 7 * npix * sizeof(double);
-	const size_t bytes = size_t(procs) * plane_bytes + size_t(procs) * sizeof(WorkerResult);
+	const size_t bytes = size_t(procs) * plane_bytes + size_t(procs) * sizeof(WorkerResult) + sizeof(WorkerShared);
 	void* shm = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
 	if (shm == MAP_FAILED) die("--procs", "mmap of the shared accumulators failed");
 	double* sums = static_cast<double*>(shm);
 	WorkerResult* res = reinterpret_cast<WorkerResult*>(static_cast<char*>(shm) + size_t(procs) * plane_bytes);
+	WorkerShared* shared = reinterpret_cast<WorkerShared*>(res + procs);        // zero-filled by mmap
+	const bool staggered = s.overlap_init;
+	const int block = 32;                    // frames per pull in the staggered mode
 	std::vector<pid_t> pids;
 	for (int g = 0; g < procs; ++g) {
 		const int base = frames / procs, rem = frames % procs;
@@ -327,42 +348,77 @@ void run_processes(State& s, int procs, int frames, std::chrono::steady_clock::t
 		if (pid < 0) die("--procs", "fork failed");
 		if (pid == 0) {
 			WorkerResult& r = res[g];
+			bool holds_turn = false;
 			auto bail = [&](const char* what, const char* detail) {
 				std::snprintf(r.error, sizeof(r.error), "%s: %s", what, detail ? detail : "");
+				if (holds_turn) __sync_fetch_and_add(&shared->turn, 1);      // never leave the others waiting
 				_exit(2);
 			};
 			setenv("CUDA_VISIBLE_DEVICES", dev.c_str(), 1);
+			if (staggered) {
+				// The driver initialises one process at a time whatever we do (eight starting at once each take 9.4 s on an
+				// 8 x B200 box, one alone 0.7 s: profiles/r2s_startup_probe_8gpu.log), so the workers queue up explicitly:
+				// worker g makes its first CUDA call when worker g - 1 has its context, and starts rendering at once.
+				while (*const_cast<volatile int*>(&shared->turn) != g) usleep(200);
+				holds_turn = true;
+			}
 			mcpt_params p{};
 			p.width = s.cfg.width; p.height = s.cfg.height; p.max_depth = s.cfg.maxdepth; p.max_attempt = s.cfg.attempt;
 			p.device = 0; p.seed_mode = 1; p.sampling = s.mis ? (s.mis_ratio ? MCPT_SAMPLING_NEE_MIS_RATIO : MCPT_SAMPLING_NEE_MIS) : MCPT_SAMPLING_REFERENCE;
 			p.run_seed = s.run_seed; p.traversal = MCPT_TRAVERSAL_FAST;
+			auto w0 = std::chrono::steady_clock::now();
 			mcpt_ctx* c = mcpt_create(&p);
 			if (!c) bail("mcpt_create", mcpt_last_error());
+			r.create_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
+			if (staggered) { __sync_fetch_and_add(&shared->turn, 1); holds_turn = false; }
 			int rc = s.derived ? mcpt_upload_scene_derived(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()), s.derived, s.derived_bytes, 0)
 			                   : mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
 			if (rc || mcpt_set_camera(c, &s.cfg.camera)) bail("scene upload", mcpt_last_error());
 			r.ready_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-			if (count > 0 && (mcpt_set_first_sample(c, uint32_t(first)) || mcpt_render(c, count))) bail("mcpt_render", mcpt_last_error());
+			r.upload_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count() - r.create_s;
+			if (staggered) {
+				// blocks of sample indices from a shared counter: whoever is ready first renders most (seed_mode 1 makes a
+				// sample a function of its index alone, so the set of samples - not their owner - defines the image)
+				for (;;) {
+					const int b0 = __sync_fetch_and_add(&shared->next_block, block);
+					if (b0 >= frames) break;
+					if (mcpt_set_first_sample(c, uint32_t(b0)) || mcpt_render(c, std::min(block, frames - b0))) bail("mcpt_render", mcpt_last_error());
+				}
+			} else if (count > 0 && (mcpt_set_first_sample(c, uint32_t(first)) || mcpt_render(c, count))) bail("mcpt_render", mcpt_last_error());
 			if (mcpt_read_sums(c, sums + size_t(g) * 7 * npix)) bail("readback", mcpt_last_error());
 			mcpt_stats st{};
 			mcpt_get_stats(c, &st);
 			r.rays = st.rays_traced; r.paths = st.paths;
 			r.done_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-			r.ok = 1;
+			__sync_synchronize();          // the sums and the record above are visible before the flag
+			*const_cast<volatile int*>(&r.ok) = 1;
 			_exit(0);      // no destructors: the driver tears the context down with the process
 		}
 		pids.push_back(pid);
 	}
+	// A worker's sums are complete when it sets `ok` (its last store before _exit); its process then spends another
+	// second or two tearing its CUDA context down, which the image does not have to wait for: poll the flags, notice
+	// early deaths through waitpid(WNOHANG), reap everybody at the very end (reap_workers).
 	bool failed = false;
-	for (int g = 0; g < procs; ++g) {
-		int status = 0;
-		waitpid(pids[size_t(g)], &status, 0);
-		if (!WIFEXITED(status) || WEXITSTATUS(status) != 0 || !res[g].ok) {
-			std::fprintf(stderr, "mcpt: worker %d failed: %s\n", g, res[g].error[0] ? res[g].error : "(killed)");
-			failed = true;
+	std::vector<char> finished(size_t(procs), 0), reaped(size_t(procs), 0);
+	for (int left = procs; left > 0 && !failed;) {
+		for (int g = 0; g < procs; ++g) {
+			if (finished[size_t(g)]) continue;
+			if (*const_cast<volatile int*>(&res[g].ok)) { finished[size_t(g)] = 1; --left; continue; }
+			int status = 0;
+			if (!reaped[size_t(g)] && waitpid(pids[size_t(g)], &status, WNOHANG) == pids[size_t(g)]) {
+				reaped[size_t(g)] = 1;
+				if (!*const_cast<volatile int*>(&res[g].ok)) {
+					std::fprintf(stderr, "mcpt: worker %d failed: %s\n", g, res[g].error[0] ? res[g].error : "(killed)");
+					failed = true;
+				}
+			}
 		}
+		if (left > 0) usleep(500);
 	}
 	if (failed) std::exit(1);
+	__sync_synchronize();
+	for (int g = 0; g < procs; ++g) if (!reaped[size_t(g)]) g_unreaped.push_back(pids[size_t(g)]);
 	all_ready_s = first_ready_s = res[0].ready_s;
 	render_done_s = res[0].done_s;
 	for (int g = 0; g < procs; ++g) {
@@ -371,6 +427,8 @@ void run_processes(State& s, int procs, int frames, std::chrono::steady_clock::t
 		render_done_s = std::max(render_done_s, res[g].done_s);
 		tot.rays_traced += res[g].rays;
 		tot.paths += res[g].paths;
+		s.create_s = std::max(s.create_s, res[g].create_s);
+		s.upload_s = std::max(s.upload_s, res[g].upload_s);
 	}
 	acc.resize(7 * npix);
 	const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
@@ -480,9 +538,8 @@ int main(int argc, char** argv) {
 			if (pid < 0) die("--procs", "fork failed");
 			if (pid == 0) {
 				setenv("CUDA_VISIBLE_DEVICES", visible_device(0).c_str(), 1);     // the device builders run on the first device
-				State h = s;
-				load_scene(h);
-				_exit(std::strcmp(h.cache_state, "miss") == 0 ? 0 : 3);
+				load_scene(s);               // this is the child's own copy of the state
+				_exit(std::strcmp(s.cache_state, "miss") == 0 ? 0 : 3);
 			}
 			int status = 0;
 			waitpid(pid, &status, 0);
@@ -496,7 +553,8 @@ int main(int argc, char** argv) {
 		s.load_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 		double render_done_s = 0.0;
 		run_processes(s, procs, frames, t0, acc, tot, all_ready_s, first_ready_s, render_done_s);
-		t1 = t0 + std::chrono::duration_cast<std::chrono::steady_clock::duration>(std::chrono::duration<double>(all_ready_s));
+		// render_s counts from the moment the first worker could render (staggered start) / all could (static split)
+		t1 = t0 + std::chrono::duration_cast<std::chrono::steady_clock::duration>(std::chrono::duration<double>(s.overlap_init ? first_ready_s : all_ready_s));
 		t2 = t0 + std::chrono::duration_cast<std::chrono::steady_clock::duration>(std::chrono::duration<double>(render_done_s));
 	} else {
 		init(s, gpus);
@@ -550,12 +608,13 @@ int main(int argc, char** argv) {
 	auto t4 = std::chrono::steady_clock::now();
 	double sec = std::chrono::duration<double>(t2 - t1).count();
 	std::printf("Finished Attempting\n");                                    // colorout.cpp:65
-	std::printf("{\"scene\": \"%s%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"gpus\": %d, \"procs\": %d, \"scene_cache\": \"%s\", \"load_s\": %.3f, \"init_s\": %.3f, "
+	std::printf("{\"scene\": \"%s%s\", \"width\": %d, \"height\": %d, \"frames\": %d, \"gpus\": %d, \"procs\": %d, \"scene_cache\": \"%s\", \"load_s\": %.3f, \"create_s\": %.3f, \"upload_s\": %.3f, \"init_s\": %.3f, "
 	            "\"render_s\": %.3f, \"merge_read_s\": %.3f, \"total_s\": %.3f, \"total_with_files_s\": %.3f, \"first_gpu_ready_s\": %.3f, \"all_gpus_ready_s\": %.3f, \"mrays_per_s\": %.1f, \"mpaths_per_s\": %.1f, \"out\": \"%s.hdr\"}\n",
-	            s.cfg.directory, s.cfg.objname, s.cfg.width, s.cfg.height, frames, gpus, procs > 1 ? procs : 1, s.cache_state, s.load_s,
+	            s.cfg.directory, s.cfg.objname, s.cfg.width, s.cfg.height, frames, gpus, procs > 1 ? procs : 1, s.cache_state, s.load_s, s.create_s, s.upload_s,
 	            std::chrono::duration<double>(t1 - t0).count(), sec, std::chrono::duration<double>(t3 - t2).count(), std::chrono::duration<double>(t3 - t0).count(),
 	            std::chrono::duration<double>(t4 - t0).count(), first_ready_s, all_ready_s, tot.rays_traced / sec / 1e6, tot.paths / sec / 1e6, base.c_str());
 	for (mcpt_ctx* c : s.ctx) mcpt_destroy(c);
+	reap_workers();
 	mcpt_host_free(s.tris);
 	mcpt_host_free(s.mats);
 	mcpt_host_free(s.mat_ids);

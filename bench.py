@@ -26,6 +26,8 @@ work is fixed, ranks own disjoint sample indices, scene + BVH replicated).
              the same workload through k_pixel_chain, and frame by frame as OpenCL::update would call it.
   strong_scaling      a fixed total of samples split over the ranks by sharding.sample_range, timed from the first
              launch to the merged sums on rank 0 (max over ranks); init (context + upload) reported beside it.
+  scene_load          start-up either side of the path (SURVEY f-2): OBJ/MTL -> resident scene cold (parallel parse, device
+             LBVH, host layout derivation) against a hit of the binary scene cache, N = 1 only.
   cpu_baseline / --impl reference: the reference's OWN kernels (kernels/*.cl + objdef.h compiled as C++,
              oracle/_ref/libmcpt_refcl.so; the oracle port only where that was never built) on all host
              cores, on a bounded sample of the same workload (960x540 view, same camera/scene/depth).
@@ -59,8 +61,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--depth", type=int, default=16)
-    ap.add_argument("--spp-per-step", type=int, default=16)
-    ap.add_argument("--samples-in-flight", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=64)
+    ap.add_argument("--samples-in-flight", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the scenes / reference_seeding / strong_scaling sections (A/B runs)")
     ap.add_argument("--strong-spp", type=int, default=4096, help="total samples of the strong-scaling section (BASELINE configs[4]: 4096)")
@@ -76,7 +78,7 @@ def workload_config(a, n):
             "scene": a.scene, "resolution": [a.width, a.height], "max_depth": a.depth,
             "spp_per_step_per_gpu": a.spp_per_step, "parallelism": "sample-sharded x%d" % n,
             "samples_in_flight": a.samples_in_flight,
-            "l2": "per-step path-state + sample streams (about 4 GB at 16 samples in flight) exceed the 126 MB L2; scene is meant to stay L2-resident"}
+            "l2": "per-step path-state + sample streams (%.0f GB at %d samples in flight) exceed the 126 MB L2; scene is meant to stay L2-resident" % (a.samples_in_flight * a.width * a.height * 136 / 1e9, a.samples_in_flight)}
 
 
 # ---------------------------------------------------------------------------- CPU side
@@ -290,6 +292,43 @@ def scene_section(name, w, h, depth, spp, reps, local, torch):
     return {"workload": "Scene/%s %dx%d, max depth %d, %d x %d spp" % (name, w, h, depth, reps, spp),
             "mrays_per_s": st["rays_traced"] / ms / 1e3, "mpaths_per_s": st["paths"] / ms / 1e3,
             "rays_per_path": st["rays_traced"] / max(1, st["paths"]), "ms": ms, "gpu_launches": st["kernel_launches"]}
+
+
+def scene_load_section(a, local):
+    """start-up either side of the hot path - OBJ/MTL to a resident scene, cold (parallel parse, device
+    LBVH, layout derivation on the host) against a hit of the binary scene cache (one file read + its checksum)."""
+    import tempfile
+    from montecarlopathtracing_b200 import device, host, scenes
+    d, obj, _, _ = scenes.SCENES[a.scene]
+    directory = scenes.scene_dir(a.scene)
+    t0 = time.perf_counter()
+    fresh = host.load_object(directory, obj, threads=0)
+    t1 = time.perf_counter()
+    nodes = device.build_lbvh(fresh.triangles, device=local)
+    t2 = time.perf_counter()
+    blob = device.derive_scene(fresh.triangles, fresh.materials, nodes)
+    t3 = time.perf_counter()
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, "scene.mcptcache")
+        key = host.scene_key(directory, obj, "hlbvh")
+        t4 = time.perf_counter()
+        host.cache_store(path, key, fresh, nodes, blob)
+        t5 = time.perf_counter()
+        key2 = host.scene_key(directory, obj, "hlbvh")
+        got, got_nodes, got_blob = host.cache_load(path, key2)
+        t6 = time.perf_counter()
+        size = os.path.getsize(path)
+    with device.Context(a.width, a.height, a.depth, 1 << 30, device=local, seed_mode=1) as c:
+        c.synchronize()
+        t7 = time.perf_counter()
+        c.upload_scene(got.triangles, got.materials, got_nodes, derived=got_blob)
+        c.synchronize()
+        t8 = time.perf_counter()
+    same = (got.triangles.tobytes() == fresh.triangles.tobytes() and got_nodes.tobytes() == nodes.tobytes() and got_blob == blob)
+    return {"scene": a.scene, "triangles": int(len(fresh.triangles)),
+            "cold": {"parse_s": t1 - t0, "device_lbvh_s": t2 - t1, "derive_layout_s": t3 - t2, "total_s": t3 - t0},
+            "cache": {"key_and_store_s": t5 - t3, "key_and_load_s": t6 - t5, "file_bytes": int(size), "equal_to_fresh": bool(same)},
+            "upload_with_cached_layout_s": t8 - t7}
 
 
 def reference_seeding_section(a, sc, local, torch):
@@ -544,6 +583,7 @@ def run_b200(a):
         out["scenes"] = {"cbox": scene_section("cbox", 1024, 1024, 8, 64, 2, local, torch),
                          "veach_mis": scene_section("veach_mis", 1280, 720, 16, 64, 2, local, torch)}
         out["reference_seeding"] = reference_seeding_section(a, sc, local, torch)
+        out["scene_load"] = scene_load_section(a, local)
     if rank == 0:
         if world == 1 and not a.no_cpu_baseline:
             base, _, _, _, image = cpu_sample(a)

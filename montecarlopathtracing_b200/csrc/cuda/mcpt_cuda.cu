@@ -1244,13 +1244,15 @@ int mcpt_render_async(mcpt_ctx* c, int spp) {
 		return fail(MCPT_ERR_STATE, "mcpt_render: the NEE + MIS mode needs the fast walk, which this scene cannot use (single triangle or boxes not nested)");
 	int S = c->prm.seed_mode == 0 ? 1 : c->prm.samples_in_flight;
 	if (S <= 0) {
-		// automatic: about 32 Mi paths in flight (120 B each), never more than a quarter of the free memory.  Large
-		// waves matter: every bounce launch ends with a tail in which the persistent blocks run dry one by one
-		// (measured at 1080p, depth 16: 2 samples in flight 2836 Mrays/s, 8: 3285, 16: 3370, 32: 3430)
+		// automatic: about 128 Mi paths in flight (120 B each + 16 B of sort keys / permutation), never more than a
+		// quarter of the free memory.  Large waves matter twice: every bounce launch ends with a tail in which the
+		// persistent blocks run dry one by one, and the coherence sort finds closer neighbours in a denser population
+		// (measured at 1080p, depth 16, sorted queues: 8 samples in flight 3 829 Mrays/s, 16: 4 070, 32: 4 202,
+		// 64: 4 283; profiles/r2q_wave_size.log)
 		size_t free_b = 0, total_b = 0;
 		CU(cudaMemGetInfo(&free_b, &total_b));
-		long paths = 32L << 20;
-		if (c->wave_samples == 0 && size_t(paths) * 120 > free_b / 4) paths = long(free_b / 4 / 120);
+		long paths = 128L << 20;
+		if (c->wave_samples == 0 && size_t(paths) * 136 > free_b / 4) paths = long(free_b / 4 / 136);
 		S = int(paths / c->npix);
 		if (S < 1) S = 1;
 		if (S > 64) S = 64;

@@ -111,7 +111,15 @@ def test_one_process_per_device_equals_the_in_process_merge(tmp_path, cbox):
         b.render(4)
         a.merge_sums([b])
         img = device.image_from_sums(a.read_sums(), w, h)
-    host.write_hdr(str(tmp_path / "ref.hdr"), img)
+        host.write_hdr(str(tmp_path / "ref.hdr"), img)
+        # --overlap-init: the workers initialise CUDA one after the other and pull blocks of 32 frames from a shared
+        # counter; these 9 frames are one block, so one worker renders them all and the other contributes zeros
+        a.reset_accumulation()
+        a.render(9)
+        host.write_hdr(str(tmp_path / "ref_one.hdr"), device.image_from_sums(a.read_sums(), w, h))
     ref = _bytes(str(tmp_path / "ref.hdr"))
     for state in ("off", "miss", "hit"):
         assert _bytes(str(tmp_path / ("p_" + state + ".hdr"))) == ref, state
+    line = _run(["--config", cfg, "--out", str(tmp_path / "stag"), "--seed", "12", "--procs", "2", "--overlap-init"], env=env)
+    assert line["procs"] == 2 and line["first_gpu_ready_s"] <= line["all_gpus_ready_s"]
+    assert _bytes(str(tmp_path / "stag.hdr")) == _bytes(str(tmp_path / "ref_one.hdr"))
