@@ -93,3 +93,29 @@ def test_bench_seeded_render_equals_the_oracle(dining):
     assert np.array_equal(sums[6], ref["counts"].astype(np.float64))
     assert sums[:3].tobytes() == np.ascontiguousarray(ref["sum"].T).tobytes()
     assert sums[3:6].tobytes() == np.ascontiguousarray(ref["sumsq"].T).tobytes()
+
+
+@pytest.mark.parametrize("name,w,h,depth,spp", [("cbox", 1024, 1024, 8, 2), ("mis", 1280, 720, 16, 3)])
+def test_other_baseline_configs_at_full_size_equal_the_reference_frame_loop(name, w, h, depth, spp, request):
+    """BASELINE configs[2] (cbox 1024x1024, depth 8) and configs[3] (veach_mis 1280x720, depth 16) at their full frame
+    sizes, reference seeding: running mean, counts, seeds and ray count of mcpt_render equal OpenCL::update driven over
+    the reference's own kernels, bit for bit.  veach_mis is the glossy scene (Ns up to 4000): every Phong pow of the
+    render goes through cr_pow and the rescaled throughput division (mcpt_device.cuh)."""
+    assert O.refcl() is not None
+    O.refcl().refcl_set_threads(os.cpu_count() or 1)
+    sc = request.getfixturevalue(name)
+    seeds = O.init_seeds(w * h, 11)
+    hist = np.zeros((w * h, 4), np.float32)
+    counts = np.zeros(w * h, np.int32)
+    traced = O.refcl_update(sc.camera, w, h, sc.nodes, sc.triangles, sc.materials, depth, 1 << 20, spp, seeds, hist, counts)
+    with device.Context(w, h, depth, 1 << 20, seed_mode=0, run_seed=11) as ctx:
+        ctx.upload_scene(sc.triangles, sc.materials, sc.nodes)
+        ctx.set_camera(sc.camera)
+        ctx.render(spp)
+        g_hist, g_counts = ctx.read_history()
+        g_seeds = ctx.read_seeds()
+        st = ctx.stats()
+    assert np.array_equal(g_counts, counts) and counts.sum() > 0
+    assert g_hist.view(np.uint32).tobytes() == hist.view(np.uint32).tobytes()
+    assert np.array_equal(g_seeds, seeds)
+    assert st["rays_traced"] == traced and st["paths"] == spp * w * h
