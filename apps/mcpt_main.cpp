@@ -119,6 +119,11 @@ mcpt_ctx* make_context(const State& s, int g, int ngpus) {
 	int rc = s.derived ? mcpt_upload_scene_derived(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()),
 	                                                s.derived, s.derived_bytes, 0)
 	                   : mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
+	if (rc && s.derived) {
+		// a cached layout this library does not accept (written by another version of the builder): derive it afresh
+		std::fprintf(stderr, "mcpt: cached traversal layout not used (%s)\n", mcpt_last_error());
+		rc = mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
+	}
 	if (rc || mcpt_set_camera(c, &s.cfg.camera)) die("scene upload", mcpt_last_error());
 	auto t2 = std::chrono::steady_clock::now();
 	{
@@ -373,6 +378,7 @@ void run_processes(State& s, int procs, int frames, std::chrono::steady_clock::t
 			if (staggered) { __sync_fetch_and_add(&shared->turn, 1); holds_turn = false; }
 			int rc = s.derived ? mcpt_upload_scene_derived(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()), s.derived, s.derived_bytes, 0)
 			                   : mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
+			if (rc && s.derived) rc = mcpt_upload_scene(c, s.tris, s.ntris, s.mats, s.nmats, s.nodes.data(), int(s.nodes.size()));
 			if (rc || mcpt_set_camera(c, &s.cfg.camera)) bail("scene upload", mcpt_last_error());
 			r.ready_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 			r.upload_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count() - r.create_s;

@@ -89,6 +89,12 @@ SceneKey scene_key(const std::string& directory, const std::string& objname, con
 std::string scene_cache_path(const std::string& directory, const std::string& objname, const std::string& bvhtype);
 void scene_cache_store(const std::string& path, const SceneKey& key, const CachedScene& scene);      // throws on I/O errors
 bool scene_cache_load(const std::string& path, const SceneKey& key, CachedScene& scene, std::string* why_not = nullptr);
+// The same, into malloc'ed buffers the caller releases with free() (what the C ABI hands out): no intermediate copies.
+struct RawScene {
+	mcpt_triangle* triangles; mcpt_material* materials; int* material_ids; mcpt_bvh_node* nodes; unsigned char* derived;
+	int ntris, nmats, nnodes; size_t derived_bytes; bool with_normals;
+};
+bool scene_cache_load_raw(const std::string& path, const SceneKey& key, RawScene& scene, std::string* why_not = nullptr);
 
 // ------------------------------------------------------------------ BVH
 // LBVH (BVH/hlbvh.cpp:92-200): 30-bit Morton of AABB centroids, stable sort, split at the

@@ -98,21 +98,16 @@ int mcpt_host_cache_load(const char* path, const mcpt_scene_key* key, mcpt_trian
                          mcpt_material** mats, int* nmats, int** material_ids, mcpt_bvh_node** nodes, int* nnodes,
                          void** derived, size_t* derived_bytes) {
 	return guarded([&] {
-		CachedScene s;
+		RawScene s{};
 		std::string why;
-		if (!scene_cache_load(path, SceneKey{{key->h[0], key->h[1]}}, s, &why)) {
+		if (!scene_cache_load_raw(path, SceneKey{{key->h[0], key->h[1]}}, s, &why)) {
 			g_err = why;
 			return 1;
 		}
-		*ntris = int(s.triangles.size());
-		*nmats = int(s.materials.size());
-		*nnodes = int(s.nodes.size());
-		*tris = dup(s.triangles);
-		*mats = dup(s.materials);
-		*material_ids = dup(s.material_ids);
-		*nodes = dup(s.nodes);
-		if (derived) *derived = dup(s.derived);
-		if (derived_bytes) *derived_bytes = s.derived.size();
+		*ntris = s.ntris; *nmats = s.nmats; *nnodes = s.nnodes;
+		*tris = s.triangles; *mats = s.materials; *material_ids = s.material_ids; *nodes = s.nodes;
+		if (derived) *derived = s.derived; else std::free(s.derived);
+		if (derived_bytes) *derived_bytes = s.derived_bytes;
 		return 0;
 	});
 }

@@ -148,7 +148,7 @@ void scene_cache_store(const std::string& path, const SceneKey& key, const Cache
 	}
 }
 
-bool scene_cache_load(const std::string& path, const SceneKey& key, CachedScene& s, std::string* why) {
+bool scene_cache_load_raw(const std::string& path, const SceneKey& key, RawScene& s, std::string* why) {
 	auto miss = [&](const std::string& m) { if (why) *why = m; return false; };
 	File in;
 	in.f = std::fopen(path.c_str(), "rb");
@@ -165,27 +165,39 @@ bool scene_cache_load(const std::string& path, const SceneKey& key, CachedScene&
 	                      uint64_t(h.nmats) * sizeof(mcpt_material) + uint64_t(h.nnodes) * sizeof(mcpt_bvh_node) + h.derived_bytes;
 	if (size != want) return miss("file size does not match its header");
 	std::fseek(in.f, long(sizeof(Header)), SEEK_SET);
-	CachedScene t;
-	t.with_normals = h.with_normals != 0;
-	t.triangles.resize(size_t(h.ntris));
-	t.materials.resize(size_t(h.nmats));
-	t.material_ids.resize(size_t(h.ntris));
-	t.nodes.resize(size_t(h.nnodes));
-	t.derived.resize(size_t(h.derived_bytes));
-	auto get = [&](void* p, size_t n) { return n == 0 || std::fread(p, 1, n, in.f) == n; };
-	if (!get(t.triangles.data(), t.triangles.size() * sizeof(mcpt_triangle)) ||
-	    !get(t.materials.data(), t.materials.size() * sizeof(mcpt_material)) ||
-	    !get(t.material_ids.data(), t.material_ids.size() * sizeof(int)) ||
-	    !get(t.nodes.data(), t.nodes.size() * sizeof(mcpt_bvh_node)) || !get(t.derived.data(), t.derived.size()))
-		return miss("short read");
+	// every section is read straight into the buffer the caller will own (mcpt_host_free): one copy of 200 MB, not three
+	const size_t bytes[5] = {size_t(h.ntris) * sizeof(mcpt_triangle), size_t(h.nmats) * sizeof(mcpt_material),
+	                         size_t(h.ntris) * sizeof(int), size_t(h.nnodes) * sizeof(mcpt_bvh_node), size_t(h.derived_bytes)};
+	void* buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+	auto release = [&] { for (void*& b : buf) { std::free(b); b = nullptr; } };
 	Hash128 ph;
-	hash_update(ph, t.triangles.data(), t.triangles.size() * sizeof(mcpt_triangle));
-	hash_update(ph, t.materials.data(), t.materials.size() * sizeof(mcpt_material));
-	hash_update(ph, t.material_ids.data(), t.material_ids.size() * sizeof(int));
-	hash_update(ph, t.nodes.data(), t.nodes.size() * sizeof(mcpt_bvh_node));
-	hash_update(ph, t.derived.data(), t.derived.size());
-	if (ph.a != h.payload_hash[0] || ph.b != h.payload_hash[1]) return miss("payload checksum mismatch (corrupt file)");
-	s = std::move(t);
+	for (int k = 0; k < 5; ++k) {
+		buf[k] = std::malloc(bytes[k] + 1);
+		if (!buf[k]) { release(); return miss("out of memory"); }
+		if (bytes[k] && std::fread(buf[k], 1, bytes[k], in.f) != bytes[k]) { release(); return miss("short read"); }
+		hash_update(ph, buf[k], bytes[k]);
+	}
+	if (ph.a != h.payload_hash[0] || ph.b != h.payload_hash[1]) { release(); return miss("payload checksum mismatch (corrupt file)"); }
+	s.triangles = static_cast<mcpt_triangle*>(buf[0]);
+	s.materials = static_cast<mcpt_material*>(buf[1]);
+	s.material_ids = static_cast<int*>(buf[2]);
+	s.nodes = static_cast<mcpt_bvh_node*>(buf[3]);
+	s.derived = static_cast<unsigned char*>(buf[4]);
+	s.ntris = h.ntris; s.nmats = h.nmats; s.nnodes = h.nnodes; s.derived_bytes = size_t(h.derived_bytes);
+	s.with_normals = h.with_normals != 0;
+	return true;
+}
+
+bool scene_cache_load(const std::string& path, const SceneKey& key, CachedScene& s, std::string* why) {
+	RawScene r{};
+	if (!scene_cache_load_raw(path, key, r, why)) return false;
+	s.with_normals = r.with_normals;
+	s.triangles.assign(r.triangles, r.triangles + r.ntris);
+	s.materials.assign(r.materials, r.materials + r.nmats);
+	s.material_ids.assign(r.material_ids, r.material_ids + r.ntris);
+	s.nodes.assign(r.nodes, r.nodes + r.nnodes);
+	s.derived.assign(r.derived, r.derived + r.derived_bytes);
+	std::free(r.triangles); std::free(r.materials); std::free(r.material_ids); std::free(r.nodes); std::free(r.derived);
 	return true;
 }
 

@@ -121,10 +121,13 @@ def cache_load(path, key):
     if rc == 1:
         return None
     try:
-        tris = np.frombuffer(ctypes.string_at(tr, nt.value * 64), dtype=T.TRIANGLE).copy()
-        mats = np.frombuffer(ctypes.string_at(mt, nm.value * 48), dtype=T.MATERIAL).copy()
-        mids = np.frombuffer(ctypes.string_at(ids, nt.value * 4), dtype=np.int32).copy()
-        nodes = np.frombuffer(ctypes.string_at(nd, nn.value * 64), dtype=T.BVH_NODE).copy()
+        def view(ptr, nbytes, dtype):       # one copy out of the malloc'ed buffer
+            addr = ctypes.cast(ptr, ctypes.c_void_p).value
+            return np.frombuffer((ctypes.c_char * nbytes).from_address(addr), dtype=dtype).copy() if nbytes else np.zeros(0, dtype)
+        tris = view(tr, nt.value * 64, T.TRIANGLE)
+        mats = view(mt, nm.value * 48, T.MATERIAL)
+        mids = view(ids, nt.value * 4, np.int32)
+        nodes = view(nd, nn.value * 64, T.BVH_NODE)
         derived = ctypes.string_at(dv, nb.value)
     finally:
         for p in (tr, mt, ids, nd, dv):
