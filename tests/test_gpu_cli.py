@@ -123,3 +123,19 @@ def test_one_process_per_device_equals_the_in_process_merge(tmp_path, cbox):
     line = _run(["--config", cfg, "--out", str(tmp_path / "stag"), "--seed", "12", "--procs", "2", "--overlap-init"], env=env)
     assert line["procs"] == 2 and line["first_gpu_ready_s"] <= line["all_gpus_ready_s"]
     assert _bytes(str(tmp_path / "stag.hdr")) == _bytes(str(tmp_path / "ref_one.hdr"))
+
+
+def test_a_refused_cached_layout_falls_back_to_a_fresh_derivation(tmp_path):
+    """A cache file whose arrays are current but whose traversal layout was written by another builder version (here:
+    a blob with a foreign header) must not stop the renderer: the layout is derived afresh and the image is the same."""
+    cfg, directory, obj = _config(tmp_path, "cbox", 64, 48, 8, 2)
+    _run(["--config", cfg, "--out", str(tmp_path / "a"), "--seed", "3", "--no-cache"])
+    sc = host.load_object(directory, obj)
+    nodes = host.build_bvh(sc.triangles)
+    blob = bytearray(device.derive_scene(sc.triangles, sc.materials, nodes))
+    blob[8:12] = (999).to_bytes(4, "little")                      # the blob's version field
+    host.cache_store(host.cache_path(directory, obj, "hlbvh"), host.scene_key(directory, obj, "hlbvh"), sc, nodes, bytes(blob))
+    r = subprocess.run([EXE, "--config", cfg, "--out", str(tmp_path / "b"), "--seed", "3"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "cached traversal layout not used" in r.stderr and '"scene_cache": "hit"' in r.stdout
+    assert _bytes(str(tmp_path / "a.hdr")) == _bytes(str(tmp_path / "b.hdr"))
