@@ -306,8 +306,10 @@ def scene_load_section(a, local):
     t1 = time.perf_counter()
     nodes = device.build_lbvh(fresh.triangles, device=local)
     t2 = time.perf_counter()
-    blob = device.derive_scene(fresh.triangles, fresh.materials, nodes)
+    blob, tree_ms = device.derive_scene(fresh.triangles, fresh.materials, nodes, device=local, return_ms=True)   # what an upload of new geometry does
     t3 = time.perf_counter()
+    host_blob = device.derive_scene(fresh.triangles, fresh.materials, nodes)                                  # all on the host (mcpt_derive_scene)
+    t3h = time.perf_counter()
     with tempfile.TemporaryDirectory() as tmp:
         path = os.path.join(tmp, "scene.mcptcache")
         key = host.scene_key(directory, obj, "hlbvh")
@@ -326,7 +328,8 @@ def scene_load_section(a, local):
         t8 = time.perf_counter()
     same = (got.triangles.tobytes() == fresh.triangles.tobytes() and got_nodes.tobytes() == nodes.tobytes() and got_blob == blob)
     return {"scene": a.scene, "triangles": int(len(fresh.triangles)),
-            "cold": {"parse_s": t1 - t0, "device_lbvh_s": t2 - t1, "derive_layout_s": t3 - t2, "total_s": t3 - t0},
+            "cold": {"parse_s": t1 - t0, "device_lbvh_s": t2 - t1, "derive_layout_s": t3 - t2, "fast_tree_device_ms": tree_ms,
+                     "total_s": t3 - t0, "derive_layout_on_host_s": t3h - t3, "device_tree_equals_host_tree": bool(host_blob == blob)},
             "cache": {"key_and_store_s": t5 - t3, "key_and_load_s": t6 - t5, "file_bytes": int(size), "equal_to_fresh": bool(same)},
             "upload_with_cached_layout_s": t8 - t7}
 

@@ -96,7 +96,9 @@ void* mcpt_stream(mcpt_ctx* ctx);                           /* the cudaStream_t 
 int mcpt_synchronize(mcpt_ctx* ctx);
 
 /* Host arrays are borrowed for the call and copied.  nodes = the canonical BVHNode[2n-1] of
- * mcpt_host_build_bvh (reference layout); the device traversal layout is derived here. */
+ * mcpt_host_build_bvh (reference layout); the device traversal layout is derived here - for geometry the process has
+ * not seen before that includes a binned-SAH tree over the same leaves, built on the context's device
+ * (csrc/cuda/sah_build.cu; byte-identical to the host builder behind mcpt_derive_scene). */
 int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes);
 /* Same, with the caller's generation counter for the geometry: a non-zero tag equal to the previous upload's tag tells
@@ -113,6 +115,10 @@ int mcpt_upload_scene_tagged(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris
  * range (MCPT_ERR_ARG otherwise - the caller then falls back to mcpt_upload_scene); results are identical. */
 int mcpt_derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                       const mcpt_bvh_node* nodes, int nnodes, void** blob, size_t* bytes);
+/* The same blob, byte for byte, with the binned-SAH tree of the fast walk built on `device` (csrc/cuda/sah_build.cu) - what
+ * mcpt_upload_scene itself does for geometry it has not seen before; *tree_ms (optional) = device time of that build. */
+int mcpt_derive_scene_device(int device, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                             const mcpt_bvh_node* nodes, int nnodes, void** blob, size_t* bytes, float* tree_ms);
 void mcpt_free_blob(void* blob);
 int mcpt_upload_scene_derived(mcpt_ctx* ctx, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
                               const mcpt_bvh_node* nodes, int nnodes, const void* blob, size_t bytes, uint64_t geometry_tag);

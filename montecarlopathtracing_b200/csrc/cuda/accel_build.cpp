@@ -158,8 +158,10 @@ void build_sah_bvh2(const DLeaf* leaves, int ntris, std::vector<DNode>& out_node
 	for (int i = 0; i < ntris; ++i) {
 		const DLeaf& l = leaves[i];
 		Box& x = b.tri_box[size_t(i)];
-		x.lo[0] = l.bminx; x.lo[1] = l.bminy; x.lo[2] = l.bminz;
-		x.hi[0] = l.bmaxx; x.hi[1] = l.bmaxy; x.hi[2] = l.bmaxz;
+		// + 0.0f: a negative zero becomes a positive one, so that min / max never have to choose between the two (the
+		// device builder, sah_build.cu, reduces in another order and must arrive at the same bits)
+		x.lo[0] = l.bminx + 0.0f; x.lo[1] = l.bminy + 0.0f; x.lo[2] = l.bminz + 0.0f;
+		x.hi[0] = l.bmaxx + 0.0f; x.hi[1] = l.bmaxy + 0.0f; x.hi[2] = l.bmaxz + 0.0f;
 		for (int k = 0; k < 3; ++k) b.centroid[3 * size_t(i) + k] = 0.5f * (x.lo[k] + x.hi[k]);
 		b.idx[size_t(i)] = i;
 	}

@@ -104,6 +104,29 @@ const std::vector<float>& phong_accept_table() {
 	return tab;
 }
 
+// fn(lo, hi) over [0, n) on up to 8 host threads (the per-triangle / per-node loops of derive_scene)
+template <class F>
+static void parallel_ranges(int n, F&& fn) {
+	const unsigned nt = unsigned(std::min<long>(std::min(8u, std::max(1u, std::thread::hardware_concurrency())), (long(n) + 16383) / 16384));
+	if (nt <= 1) { fn(0, n); return; }
+	std::vector<std::thread> th;
+	for (unsigned t = 0; t < nt; ++t) th.emplace_back([&, t] { fn(int(long(n) * t / nt), int(long(n) * (t + 1) / nt)); });
+	for (auto& x : th) x.join();
+}
+
+// Everything mcpt_upload_scene derives from the geometry alone (leaf records, two-box nodes of the reference
+// topology, the binned-SAH tree of the fast walk).  Kept per process for the last scene, so that the N contexts of
+// a multi-GPU run derive it once (the SAH build is the expensive part of an upload).
+struct DerivedScene {
+	std::vector<mcpt_triangle> tris;      // the inputs it was derived from (compared byte for byte)
+	std::vector<mcpt_bvh_node> nodes;
+	int nmats = 0;
+	std::vector<DLeaf> dt;
+	std::vector<DNode> dn, fast;
+	bool contained = true;
+	int fast_depth = 0;
+};
+
 struct mcpt_ctx {
 	mcpt_params prm{};
 	cudaStream_t stream = nullptr;
@@ -159,6 +182,7 @@ struct mcpt_ctx {
 	// coherence order of the bounce queues (mcpt_kernels.cuh): keys written by the shade kernel, sorted by CUB, the
 	// resulting permutation read by the next walk
 	bool sort_queues = true;               // env MCPT_SORT=0 switches it off (A/B)
+	bool host_tree = false;                // env MCPT_HOST_TREE=1: the fast walk's tree from the host builder instead of sah_build.cu (same bytes)
 	DevBuf<uint32_t> sort_keys, sort_keys_out, sort_iota, sort_perm;
 	DevBuf<unsigned char> sort_temp;
 	size_t sort_temp_bytes = 0;
@@ -181,8 +205,8 @@ struct mcpt_ctx {
 	DevBuf<mcpt_hit> t_hits;
 	DevBuf<int32_t> t_closest;
 	int opt_flags = 0, block = 128;          // development switches: env MCPT_OPT, MCPT_BLOCK
-	std::vector<mcpt_triangle> cache_tris;   // host copy of the last upload (derived-layout cache key)
-	std::vector<mcpt_bvh_node> cache_nodes;
+	std::shared_ptr<const DerivedScene> derived;   // what the resident scene was derived from / into (shared by the contexts of a
+	                                               // process): the key of the unchanged-geometry shortcut, the source of the 8-wide layout
 	uint64_t geometry_tag = 0;               // caller's generation counter of the last upload (mcpt_upload_scene_tagged)
 	uint64_t launches = 0;
 	uint64_t stage_paths = 0;
@@ -235,8 +259,6 @@ struct mcpt_ctx {
 	}
 	int traversal(int requested) const { return force_reference ? MCPT_TRAVERSAL_REFERENCE : requested; }
 	// host copies kept for the lazily built 8-wide layout (MCPT_TRAVERSAL_WIDE8, experimental)
-	std::vector<DNode> host_fast;
-	std::vector<DLeaf> host_leaves;
 	bool have_wide = false;
 	int persistent_grid(int bs) const { return nsm * (MCPT_MIN_BLOCKS * 128 / bs); }
 };
@@ -548,7 +570,7 @@ int ensure_wide(mcpt_ctx* c) {
 	if (c->have_wide) return MCPT_OK;
 	std::vector<WNode> wide;
 	std::vector<DLeaf> wide_leaves;
-	build_wide_bvh8(c->host_fast, c->host_leaves.data(), int(c->host_leaves.size()), wide, wide_leaves);
+	build_wide_bvh8(c->derived->fast, c->derived->dt.data(), int(c->derived->dt.size()), wide, wide_leaves);
 	CU(cudaStreamSynchronize(c->stream));
 	CU(c->wnodes.alloc(std::max<size_t>(1, wide.size())));
 	CU(c->wleaves.alloc(std::max<size_t>(1, wide_leaves.size())));
@@ -660,6 +682,7 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
 	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128) c->block = b; }
 	if (const char* e = std::getenv("MCPT_SORT")) c->sort_queues = std::atoi(e) != 0;      // development A/B
+	if (const char* e = std::getenv("MCPT_HOST_TREE")) c->host_tree = std::atoi(e) != 0;
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
 	ok = ok && c->rays.alloc(n) == cudaSuccess && c->hits.alloc(n) == cudaSuccess && c->closest.alloc(n) == cudaSuccess &&
@@ -748,30 +771,21 @@ static bool bytes_equal(const void* a, const void* b, size_t n) {
 	return same;
 }
 
-// Everything mcpt_upload_scene derives from the geometry alone (leaf records, two-box nodes of the reference
-// topology, the binned-SAH tree of the fast walk).  Kept per process for the last scene, so that the N contexts of
-// a multi-GPU run derive it once (the SAH build is the expensive part of an upload).
-struct DerivedScene {
-	std::vector<mcpt_triangle> tris;      // the inputs it was derived from (compared byte for byte)
-	std::vector<mcpt_bvh_node> nodes;
-	int nmats = 0;
-	std::vector<DLeaf> dt;
-	std::vector<DNode> dn, fast;
-	bool contained = true;
-	int fast_depth = 0;
-};
 static std::mutex g_derived_mutex;
 static std::shared_ptr<const DerivedScene> g_derived;
 
+// tree_device >= 0: the binned-SAH tree is built on that device (sah_build.cu; same bytes as the host builder)
 static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats, const mcpt_bvh_node* nodes,
-                 int nnodes, DerivedScene& out) {
+                 int nnodes, DerivedScene& out, int tree_device = -1, float* tree_ms = nullptr) {
 	// ---- validate + derive the traversal layout (host side, once per scene)
 	std::vector<DLeaf>& dt = out.dt;
-	dt.assign(size_t(ntris), DLeaf{});
-	std::memset(dt.data(), 0, dt.size() * sizeof(DLeaf));
-	for (int i = 0; i < ntris; ++i) {
+	dt.resize(size_t(ntris));
+	std::atomic<bool> bad_material{false};
+	parallel_ranges(ntris, [&](int lo, int hi) {
+	std::memset(dt.data() + lo, 0, size_t(hi - lo) * sizeof(DLeaf));
+	for (int i = lo; i < hi; ++i) {
 		const mcpt_triangle& t = tris[i];
-		if (t.material_id < 0 || t.material_id >= nmats) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
+		if (t.material_id < 0 || t.material_id >= nmats) { bad_material = true; return; }
 		DLeaf& d = dt[i];
 		d.v0x = t.v[0].x; d.v0y = t.v[0].y; d.v0z = t.v[0].z; d.material = t.material_id;
 		// e1 = -(v1 - v0), e2 = -(v2 - v0): the matrix rows of objdef.h:194-199
@@ -783,6 +797,8 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 		d.nx = t.nx; d.ny = t.ny; d.nz = t.nz;
 		std::memcpy(&d.pad, &i, sizeof(int));     // own index: leaf records are self-describing in any order
 	}
+	});
+	if (bad_material) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: triangle material id out of range");
 	for (int m = 0; m < nmats; ++m)
 		if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
 			return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
@@ -844,8 +860,15 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 	}
 	std::vector<DNode>& fast = out.fast;
 	fast.clear();
-	if (!root_leaf) build_sah_bvh2(dt.data(), ntris, fast);
-	else fast.assign(1, DNode{});
+	if (root_leaf) fast.assign(1, DNode{});
+	else if (tree_device >= 0) {
+		DevBuf<DLeaf> d_leaves;
+		CU(cudaSetDevice(tree_device));
+		CU(d_leaves.alloc(size_t(ntris)));
+		CU(cudaMemcpy(d_leaves.p, dt.data(), sizeof(DLeaf) * size_t(ntris), cudaMemcpyHostToDevice));
+		fast.assign(size_t(ntris) - 1, DNode{});
+		if (int r = build_sah_bvh2_device(tree_device, d_leaves.p, dt.data(), ntris, fast.data(), tree_ms)) return r;
+	} else build_sah_bvh2(dt.data(), ntris, fast);
 	// the fast walk pushes at most one entry per level and does not check its stack: verify the depth here
 	int& fast_depth = out.fast_depth;
 	fast_depth = 0;
@@ -995,6 +1018,22 @@ int mcpt_derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_material*
 	return MCPT_OK;
 }
 
+int mcpt_derive_scene_device(int device, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
+                             const mcpt_bvh_node* nodes, int nnodes, void** blob, size_t* bytes, float* tree_ms) {
+	if (!blob || !bytes) return fail(MCPT_ERR_ARG, "mcpt_derive_scene_device: null output");
+	if (int r = check_scene_args(tris, ntris, mats, nmats, nodes, nnodes)) return r;
+	DerivedScene d;
+	if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, d, device, tree_ms)) return r;
+	d.nmats = nmats;
+	const size_t n = derived_blob_bytes(d);
+	unsigned char* out = static_cast<unsigned char*>(std::malloc(n));
+	if (!out) return fail(MCPT_ERR_ARG, "mcpt_derive_scene_device: out of host memory");
+	write_derived_blob(d, nnodes, geometry_hash(tris, ntris, nodes, nnodes), out);
+	*blob = out;
+	*bytes = n;
+	return MCPT_OK;
+}
+
 void mcpt_free_blob(void* blob) { std::free(blob); }
 
 int mcpt_upload_scene_derived(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const mcpt_material* mats, int nmats,
@@ -1030,9 +1069,9 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	// A non-zero geometry_tag equal to the previous upload's is the caller's word that triangles and nodes are the same
 	// bytes (a generation counter); without one the two arrays are compared (80 MB for the diningroom stand-in).
 	const bool same_tag = tag != 0 && tag == c->geometry_tag;
-	if (c->have_scene && c->cache_tris.size() == size_t(ntris) && c->cache_nodes.size() == size_t(nnodes) &&
-	    (same_tag || (bytes_equal(c->cache_tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
-	                  bytes_equal(c->cache_nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)))) {
+	if (c->have_scene && c->derived && c->derived->tris.size() == size_t(ntris) && c->derived->nodes.size() == size_t(nnodes) &&
+	    (same_tag || (bytes_equal(c->derived->tris.data(), tris, sizeof(mcpt_triangle) * ntris) &&
+	                  bytes_equal(c->derived->nodes.data(), nodes, sizeof(mcpt_bvh_node) * nnodes)))) {
 		c->geometry_tag = tag;
 		for (int m = 0; m < nmats; ++m)
 			if (mats[m].kd.w != 0.0f || mats[m].ka_ks.w != 0.0f)
@@ -1060,7 +1099,7 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 		} else {
 			auto fresh = from_blob ? from_blob : std::make_shared<DerivedScene>();
 			if (!from_blob)
-				if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, *fresh)) return r;
+				if (int r = derive_scene(tris, ntris, mats, nmats, nodes, nnodes, *fresh, c->host_tree ? -1 : c->prm.device)) return r;
 			fresh->tris.assign(tris, tris + ntris);
 			fresh->nodes.assign(nodes, nodes + nnodes);
 			fresh->nmats = nmats;
@@ -1084,8 +1123,6 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	}
 	const bool fast_too_deep = fast_depth > STACK_SIZE;
 	// the experimental 8-wide layout is derived on first use (ensure_wide), not on every upload
-	c->host_fast = fast;
-	c->host_leaves = dt;
 	c->have_wide = false;
 	CU(cudaStreamSynchronize(c->stream));
 	for (DNode& n : fast) {      // leaf links as LEAF_FLAG | triangle: no decode in the walk's loop
@@ -1134,8 +1171,7 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 			CU(cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
 		}
 	}
-	c->cache_tris.assign(tris, tris + ntris);
-	c->cache_nodes.assign(nodes, nodes + nnodes);
+	c->derived = derived;
 	c->geometry_tag = tag;
 	c->scene = SceneDev{c->nodes_ref.p, c->tris_ref.p, c->nodes.p, c->fast_nodes, c->wnodes.p, c->wleaves.p, c->leaves, c->mats.p, c->cs_table.p, ntris, nnodes, root_leaf ? 1 : 0, c->opt_flags, max_abs};
 	for (int a = 0; a < 3; ++a) {

@@ -29,7 +29,7 @@ EXPORTS = [
     "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
     "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
-    "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived", "mcpt_phong_accept_table", "mcpt_check_failures",
+    "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived", "mcpt_phong_accept_table", "mcpt_check_failures", "mcpt_derive_scene_device",
 ]
 TRACE_NOALLOC_MAX_RAYS = 65536        # MCPT_TRACE_NOALLOC_MAX_RAYS of include/mcpt.h
 
@@ -325,9 +325,10 @@ def image_from_sums(sums, width, height):
     return img
 
 
-def derive_scene(triangles, materials, nodes):
-    """The traversal layout mcpt_upload_scene derives on the host (leaf records, two-box nodes, the binned-SAH tree of
-    the fast walk) as one relocatable blob (bytes) - what the scene cache stores next to the arrays.  Needs no GPU."""
+def derive_scene(triangles, materials, nodes, device=None, return_ms=False):
+    """The traversal layout mcpt_upload_scene derives (leaf records, two-box nodes, the binned-SAH tree of the fast
+    walk) as one relocatable blob (bytes) - what the scene cache stores next to the arrays.  device=None: all on the
+    host, needs no GPU; device=k: the tree is built on that GPU (mcpt_derive_scene_device) - the same bytes."""
     tr = np.ascontiguousarray(triangles, dtype=T.TRIANGLE)
     mt = np.ascontiguousarray(materials, dtype=T.MATERIAL)
     nd = np.ascontiguousarray(nodes, dtype=T.BVH_NODE)
@@ -335,10 +336,17 @@ def derive_scene(triangles, materials, nodes):
     L = lib()
     L.mcpt_free_blob.restype = None
     L.mcpt_free_blob.argtypes = [ctypes.c_void_p]
-    if L.mcpt_derive_scene(_vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.byref(blob), ctypes.byref(n)) != 0:
+    ms = ctypes.c_float(0.0)
+    if device is None:
+        rc = L.mcpt_derive_scene(_vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.byref(blob), ctypes.byref(n))
+    else:
+        rc = L.mcpt_derive_scene_device(int(device), _vp(tr), len(tr), _vp(mt), len(mt), _vp(nd), len(nd), ctypes.byref(blob),
+                                        ctypes.byref(n), ctypes.byref(ms))
+    if rc != 0:
         raise McptError("mcpt_derive_scene: %s" % L.mcpt_last_error().decode())
     try:
-        return ctypes.string_at(blob, n.value)
+        data = ctypes.string_at(blob, n.value)
+        return (data, ms.value) if return_ms else data
     finally:
         L.mcpt_free_blob(blob)
 

@@ -47,3 +47,45 @@ def test_duplicate_codes_and_flat_axis():
 def test_errors():
     with pytest.raises(device.McptError):
         device.build_lbvh(np.zeros(0, T.TRIANGLE))
+
+
+# ---- the binned-SAH tree of the fast walk, built on the device (csrc/cuda/sah_build.cu) ---------------------------------
+@pytest.mark.parametrize("name", ["cbox", "veach_mis", "diningroom"])
+def test_device_fast_tree_equals_the_host_builder(name):
+    """mcpt_derive_scene_device == mcpt_derive_scene byte for byte: what mcpt_upload_scene derives for new geometry is
+    the host builder's tree (accel_build.cpp), produced by level-wise kernels and one block per small subtree."""
+    from montecarlopathtracing_b200 import scenes
+    sc = scenes.load(name)
+    want = device.derive_scene(sc.triangles, sc.materials, sc.nodes)
+    got, ms = device.derive_scene(sc.triangles, sc.materials, sc.nodes, device=0, return_ms=True)
+    assert got == want
+    assert 0.0 < ms < 1000.0
+
+
+@pytest.mark.parametrize("n,kind", [(2, "random"), (3, "random"), (17, "random"), (1025, "random"), (5000, "flat"), (3000, "same"),
+                                    (20000, "lopsided"), (200000, "random")])
+def test_device_fast_tree_on_synthetic_sets(n, kind):
+    """Edge cases of the builder: tiny sets, triangles in one plane, identical triangles (no axis has extent: the median
+    rule, on the host for more than 1 024 of them), an exponentially spaced chain (lopsided splits down to the depth at
+    which the host builder switches to medians)."""
+    rng = np.random.default_rng(n)
+    tris = np.zeros(n, T.TRIANGLE)
+    if kind == "same":
+        c = np.zeros((n, 1, 3))
+    elif kind == "lopsided":
+        c = np.zeros((n, 1, 3))
+        c[:, 0, 0] = 2.0 ** (-(np.arange(n) % 120).astype(np.float64))
+        c[:, 0, 1] = rng.random(n) * 1e-3
+    else:
+        c = rng.random((n, 1, 3)) * 100.0
+    v = c + (rng.random((1, 3, 3)) if kind == "same" else rng.random((n, 3, 3))) * 2.0
+    if kind == "flat":
+        v[:, :, 1] = 5.0
+    tris["v"][:, :, :3] = v.astype(np.float32)
+    tris["material_id"] = 0
+    mats = np.zeros(1, T.MATERIAL)
+    mats["type"] = 1
+    nodes = host.build_bvh(tris)
+    want = device.derive_scene(tris, mats, nodes)
+    got = device.derive_scene(tris, mats, nodes, device=0)
+    assert got == want
