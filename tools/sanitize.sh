@@ -19,8 +19,8 @@ run() {  # tool target scale [extra sanitizer flags]
 	local t1=$(date +%s)
 	printf "%-10s %-8s scale %-5s rc=%d %4ds  %s | %s\n" $tool $target $scale $rc $((t1 - t0)) "$(grep -E 'ERROR SUMMARY|RACECHECK SUMMARY' $log | tail -1)" "$(grep -c 'target .* ok' $log) ok" >> $S
 }
-for t in treelet lbvh wave chain mis merge stage metrics; do run memcheck $t 1.0 --leak-check full; done
-for t in treelet lbvh wave chain mis merge stage metrics; do run racecheck $t 0.25; done
+for t in treelet lbvh fasttree wave chain mis merge stage metrics; do run memcheck $t 1.0 --leak-check full; done
+for t in treelet lbvh fasttree wave chain mis merge stage metrics; do run racecheck $t 0.25; done
 for t in treelet wave chain mis; do run synccheck $t 0.25; done
-for t in treelet lbvh wave chain mis merge; do run initcheck $t 0.25; done
+for t in treelet lbvh fasttree wave chain mis merge; do run initcheck $t 0.25; done
 cat $S

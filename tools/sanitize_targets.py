@@ -4,6 +4,7 @@ against the un-instrumented expectation (host builder / a second run), so a sani
   treelet   treelet_build.cu: cross-SM arrival counters + __threadfence (the reference's own kernel is racy,
             kernels/treeletBVH.cl:264-277)
   lbvh      lbvh_build.cu
+  fasttree  sah_build.cu (the fast walk's binned-SAH tree; level-wise kernels + one block per small subtree)
   wave      k_wave_generate / k_wave_trace_persistent / k_wave_shade / k_wave_resolve + the CUB sort of the bounce queues
   chain     k_pixel_chain (seed_mode 0) and the queue-based regeneration loop
   mis       k_wave_shade_mis / k_wave_nee_add
@@ -44,6 +45,14 @@ def main(target, scale):
         nodes = host.build_bvh(tris)
         got = device.optimize_treelet(nodes)
         assert got.tobytes() == host.treelet(nodes).tobytes()
+    elif target == "fasttree":
+        for n, seed in ((int(60000 * scale), 4), (900, 5), (2, 6)):
+            tris = random_triangles(n, seed)
+            tris["material_id"] = 0
+            mats = np.zeros(1, T.MATERIAL)
+            mats["type"] = 1
+            nodes = host.build_bvh(tris)
+            assert device.derive_scene(tris, mats, nodes, device=0) == device.derive_scene(tris, mats, nodes)
     elif target == "lbvh":
         tris = random_triangles(int(50000 * scale))
         assert device.build_lbvh(tris).tobytes() == host.build_bvh(tris).tobytes()

@@ -33,6 +33,14 @@ def main():
     diff = sum(device.build_lbvh(tris).tobytes() != want for _ in range(20))
     print("lbvh 200k triangles x 20 runs: %d differ from the host build" % diff)
     assert diff == 0
+    # the fast walk's tree (sah_build.cu: atomics on bins and partition cursors, order-free by construction)
+    tris["material_id"] = 0
+    mats = np.zeros(1, T.MATERIAL)
+    mats["type"] = 1
+    want = device.derive_scene(tris, mats, nodes)
+    diff = sum(device.derive_scene(tris, mats, nodes, device=0) != want for _ in range(20))
+    print("fast-walk tree 200k triangles x 20 runs: %d differ from the host builder" % diff)
+    assert diff == 0
     sc = scenes.load("cbox")
     # wave pipeline (persistent walk + shade compaction + sort), different wave sizes = different schedules
     ref = None
