@@ -11,5 +11,6 @@ constexpr unsigned FAST_TREE_BUILDER_ID = 0x00020010u;   // revision 2 (zeros of
 void build_sah_bvh2(const DLeaf* leaves, int ntris, std::vector<DNode>& out_nodes);
 // The same tree, byte for byte, built on `device` (sah_build.cu): d_leaves = the records in device memory, h_leaves = the
 // same records on the host, out = ntris - 1 nodes (ntris >= 2).  Returns MCPT_OK or an MCPT_ERR_* code.
-int build_sah_bvh2_device(int device, const DLeaf* d_leaves, const DLeaf* h_leaves, int ntris, DNode* out, float* build_ms);
+// *depth (optional) = levels of inner nodes (root = 1): what the walk's stack has to hold.
+int build_sah_bvh2_device(int device, const DLeaf* d_leaves, const DLeaf* h_leaves, int ntris, DNode* out, float* build_ms, int* depth = nullptr);
 }

@@ -835,21 +835,24 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 	const bool root_leaf = is_leaf(0);
 	std::vector<DNode>& dn = out.dn;                          // indexed by reference node id (leaf slots unused)
 	dn.assign(root_leaf ? 1 : size_t(nnodes), DNode{});
-	std::memset(dn.data(), 0, dn.size() * sizeof(DNode));
-	for (int i = 0; i < nnodes; ++i) {
+	std::atomic<int> node_error{0};
+	std::atomic<bool> nested{true};
+	parallel_ranges(nnodes, [&](int lo, int hi) {
+	if (!root_leaf) std::memset(dn.data() + lo, 0, size_t(hi - lo) * sizeof(DNode));
+	for (int i = lo; i < hi; ++i) {
 		const mcpt_bvh_node& nd = nodes[i];
-		if (nd.left < 0 || nd.right < 0) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: negative child index");
+		if (nd.left < 0 || nd.right < 0) { node_error = 1; return; }
 		if (is_leaf(i)) {
-			if (nd.left >= ntris) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: leaf triangle index out of range");
+			if (nd.left >= ntris) { node_error = 2; return; }
 			continue;
 		}
-		if (nd.left >= nnodes || nd.right >= nnodes) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: child index out of range");
+		if (nd.left >= nnodes || nd.right >= nnodes) { node_error = 3; return; }
 		const mcpt_bvh_node& L = nodes[nd.left];
 		const mcpt_bvh_node& R = nodes[nd.right];
 		for (const mcpt_bvh_node* ch : {&L, &R}) {
 			if (!(ch->bbmin.x >= nd.bbmin.x && ch->bbmin.y >= nd.bbmin.y && ch->bbmin.z >= nd.bbmin.z &&
 			      ch->bbmax.x <= nd.bbmax.x && ch->bbmax.y <= nd.bbmax.y && ch->bbmax.z <= nd.bbmax.z))
-				contained = false;
+				nested = false;
 		}
 		if (root_leaf) continue;
 		DNode& d = dn[i];
@@ -858,8 +861,14 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 		d.left = is_leaf(nd.left) ? ~L.left : nd.left;
 		d.right = is_leaf(nd.right) ? ~R.left : nd.right;
 	}
+	});
+	if (node_error == 1) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: negative child index");
+	if (node_error == 2) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: leaf triangle index out of range");
+	if (node_error == 3) return fail(MCPT_ERR_ARG, "mcpt_upload_scene: child index out of range");
+	contained = nested;
 	std::vector<DNode>& fast = out.fast;
 	fast.clear();
+	int device_depth = 0;                 // the device builder reports the depth of its tree (inner levels, root = 1)
 	if (root_leaf) fast.assign(1, DNode{});
 	else if (tree_device >= 0) {
 		DevBuf<DLeaf> d_leaves;
@@ -867,12 +876,12 @@ static int derive_scene(const mcpt_triangle* tris, int ntris, const mcpt_materia
 		CU(d_leaves.alloc(size_t(ntris)));
 		CU(cudaMemcpy(d_leaves.p, dt.data(), sizeof(DLeaf) * size_t(ntris), cudaMemcpyHostToDevice));
 		fast.assign(size_t(ntris) - 1, DNode{});
-		if (int r = build_sah_bvh2_device(tree_device, d_leaves.p, dt.data(), ntris, fast.data(), tree_ms)) return r;
+		if (int r = build_sah_bvh2_device(tree_device, d_leaves.p, dt.data(), ntris, fast.data(), tree_ms, &device_depth)) return r;
 	} else build_sah_bvh2(dt.data(), ntris, fast);
 	// the fast walk pushes at most one entry per level and does not check its stack: verify the depth here
 	int& fast_depth = out.fast_depth;
-	fast_depth = 0;
-	if (!root_leaf) {
+	fast_depth = device_depth;
+	if (!root_leaf && device_depth == 0) {
 		std::vector<std::pair<int, int>> todo{{0, 1}};
 		while (!todo.empty()) {
 			auto [node, d] = todo.back();
@@ -1111,7 +1120,7 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 			return fail(MCPT_ERR_ARG, "mcpt_upload_scene: material w lanes must be 0 (as loadObject produces them)");
 	const std::vector<DLeaf>& dt = derived->dt;
 	const std::vector<DNode>& dn = derived->dn;
-	std::vector<DNode> fast = derived->fast;        // copied: the leaf links are re-encoded below
+	const std::vector<DNode>& fast = derived->fast; // leaf links as ~triangle; re-encoded on the device after the copy
 	const bool contained = derived->contained;
 	const bool root_leaf = nodes[0].left == nodes[0].right;
 	const int fast_depth = derived->fast_depth;
@@ -1125,10 +1134,6 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	// the experimental 8-wide layout is derived on first use (ensure_wide), not on every upload
 	c->have_wide = false;
 	CU(cudaStreamSynchronize(c->stream));
-	for (DNode& n : fast) {      // leaf links as LEAF_FLAG | triangle: no decode in the walk's loop
-		if (n.left < 0) n.left = int32_t(0x80000000u | uint32_t(~n.left));
-		if (n.right < 0) n.right = int32_t(0x80000000u | uint32_t(~n.right));
-	}
 	const size_t hot_nodes_bytes = (sizeof(DNode) * fast.size() + 255) / 256 * 256;
 	const size_t hot_leaf_bytes = (sizeof(DLeaf) * size_t(ntris) + 255) / 256 * 256;
 	const size_t hot_bytes = hot_nodes_bytes + hot_leaf_bytes;
@@ -1136,6 +1141,8 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 	c->fast_nodes = reinterpret_cast<DNode*>(c->hot.p);
 	c->leaves = reinterpret_cast<DLeaf*>(c->hot.p + hot_nodes_bytes);
 	CU(cudaMemcpyAsync(c->fast_nodes, fast.data(), sizeof(DNode) * fast.size(), cudaMemcpyHostToDevice, c->stream));
+	// leaf links as LEAF_FLAG | triangle: no decode in the walk's loop
+	k_encode_leaf_links<<<blocks(long(fast.size()), 256), 256, 0, c->stream>>>(c->fast_nodes, int(fast.size()));
 	CU(c->nodes_ref.alloc(nnodes));
 	CU(c->tris_ref.alloc(ntris));
 	CU(c->nodes.alloc(dn.size()));

@@ -889,4 +889,13 @@ __global__ void __launch_bounds__(256) k_merge_sums(double* __restrict__ acc, Me
 	}
 }
 
+// leaf links of the fast tree as the builders write them (~triangle) -> LEAF_FLAG | triangle, the form the walk tests
+__global__ void k_encode_leaf_links(DNode* nodes, int n) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const int l = nodes[i].left, r = nodes[i].right;
+	if (l < 0) nodes[i].left = int32_t(0x80000000u | uint32_t(~l));
+	if (r < 0) nodes[i].right = int32_t(0x80000000u | uint32_t(~r));
+}
+
 }  // namespace mcpt

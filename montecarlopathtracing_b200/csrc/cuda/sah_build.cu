@@ -507,7 +507,7 @@ int host_median(const DLeaf* h_leaves, int* d_idx, DNode* d_nodes, const Task& t
 
 // d_leaves: the DLeaf records on `device` (their boxes are all the builder reads); h_leaves: the same records on the
 // host (median fallback of large tasks only); out: ntris - 1 nodes, memcmp-equal to build_sah_bvh2's.
-int build_sah_bvh2_device(int device, const DLeaf* d_leaves, const DLeaf* h_leaves, int ntris, DNode* out, float* build_ms) {
+int build_sah_bvh2_device(int device, const DLeaf* d_leaves, const DLeaf* h_leaves, int ntris, DNode* out, float* build_ms, int* depth) {
 	if (ntris < 2) { set_last_error("fast-tree build: needs at least two triangles"); return MCPT_ERR_ARG; }
 	TRY_(cudaSetDevice(device));
 	cudaStream_t st = nullptr;       // the legacy default stream: the calls below are ordered and the copies blocking
@@ -581,6 +581,11 @@ int build_sah_bvh2_device(int device, const DLeaf* d_leaves, const DLeaf* h_leav
 	if (build_ms) TRY_(cudaEventElapsedTime(build_ms, e0, e1));
 	cudaEventDestroy(e0); cudaEventDestroy(e1);
 	if (h_status != 0) { set_last_error("fast-tree build: internal error " + std::to_string(h_status)); return MCPT_ERR_STATE; }
+	if (depth) {
+		Lists h_lists{};
+		TRY_(cudaMemcpy(&h_lists, lists.p, sizeof(Lists), cudaMemcpyDeviceToHost));
+		*depth = h_lists.max_depth;
+	}
 	return MCPT_OK;
 }
 

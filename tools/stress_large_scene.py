@@ -28,6 +28,10 @@ except device.McptError as e:
 m = device.bvh_metrics(nodes, tris, scenes.load("cbox").camera, 256, 256)
 print("metrics: sah %.3f epo %.4f lcv %.3f (ms %.2f %.2f %.2f)" % (m["sah"], m["epo"], m["lcv"], m["ms_sah"], m["ms_epo"], m["ms_lcv"]))
 mats = scenes.load("cbox").materials
+t3 = time.time(); blob_d, tree_ms = device.derive_scene(tris, mats, nodes, device=0, return_ms=True); t4 = time.time()
+blob_h = device.derive_scene(tris, mats, nodes); t5 = time.time()
+print("layout derivation: tree on the device %.2f s (tree %.1f ms), all on the host %.2f s; equal: %s" % (t4 - t3, tree_ms, t5 - t4, blob_d == blob_h))
+del blob_d, blob_h
 with device.Context(256, 256, 8, 16) as ctx:
     t3 = time.time(); ctx.upload_scene(tris, mats, nodes); print("upload %.2f s" % (time.time() - t3))
     rays = random_rays(1 << 20, nodes)
