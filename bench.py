@@ -61,8 +61,8 @@ def parse_args():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--depth", type=int, default=16)
-    ap.add_argument("--spp-per-step", type=int, default=64)
-    ap.add_argument("--samples-in-flight", type=int, default=64)
+    ap.add_argument("--spp-per-step", type=int, default=128)
+    ap.add_argument("--samples-in-flight", type=int, default=128)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the scenes / reference_seeding / strong_scaling sections (A/B runs)")
     ap.add_argument("--strong-spp", type=int, default=4096, help="total samples of the strong-scaling section (BASELINE configs[4]: 4096)")
