@@ -213,6 +213,10 @@ int mcpt_measure_read_bandwidth(int device, size_t bytes, int iters, float* gb_p
 
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);
+/* Diagnostic: how mcpt_render orders its bounce queues.  bit 0 = the path queue is walked in coherence-sorted order,
+ * bit 1 = the shadow-ray queue of the NEE + MIS modes too; -1 = the NEE + MIS modes are still timing one wave each way
+ * (the image does not depend on the order, so the library keeps whichever is faster for the scene at hand). */
+int mcpt_get_queue_sorting(mcpt_ctx* ctx, int* out);
 
 /* ---- BVH build on the device.  Replaces BVH::HLBVH<CPU>::build (BVH/hlbvh.cpp:92-200) for
  * "bvhtype": "hlbvh": host triangles in, 2*ntris-1 host nodes out, memcmp-equal to mcpt_host_build_bvh

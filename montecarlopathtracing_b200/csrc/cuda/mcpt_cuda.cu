@@ -182,8 +182,15 @@ struct mcpt_ctx {
 	// coherence order of the bounce queues (mcpt_kernels.cuh): keys written by the shade kernel, sorted by CUB, the
 	// resulting permutation read by the next walk
 	bool sort_queues = true;               // env MCPT_SORT=0 switches it off (A/B)
+	int mis_sort_mask = 3;                 // NEE + MIS: bit 0 main queue, bit 1 shadow queue (env MCPT_SORT=1/2/3)
+	// NEE + MIS: whether the two sorts pay depends on the scene (+13 % cbox, +14 % diningroom, -9 % veach_mis), and the
+	// image does not depend on the queue order, so one wave is timed each way and the faster arrangement kept.
+	struct SortTrial { cudaEvent_t t0 = nullptr, t1 = nullptr; bool pending = false, have = false; double ms_per_path = 0.0; } mis_trial[2];
+	int mis_sort_choice = -1;              // -1 undecided; else the mask in force until the scene or the camera changes
+	bool mis_sort_tune = true;             // off when MCPT_SORT pins the mask
 	bool host_tree = false;                // env MCPT_HOST_TREE=1: the fast walk's tree from the host builder instead of sah_build.cu (same bytes)
 	DevBuf<uint32_t> sort_keys, sort_keys_out, sort_iota, sort_perm;
+	DevBuf<uint32_t> mis_skeys, mis_sperm;    // NEE + MIS modes: keys / walk order of the shadow-ray queue
 	DevBuf<unsigned char> sort_temp;
 	size_t sort_temp_bytes = 0;
 	// How many items to sort is only known on the device (qcount[d]); CUB wants it on the host.  Any prefix works (see
@@ -219,6 +226,7 @@ struct mcpt_ctx {
 
 	~mcpt_ctx() {
 		for (cudaEvent_t e : ev_counts) if (e) cudaEventDestroy(e);
+		for (SortTrial& t : mis_trial) { if (t.t0) cudaEventDestroy(t.t0); if (t.t1) cudaEventDestroy(t.t1); }
 		if (h_counts) cudaFreeHost(h_counts);
 		for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
 		if (ev_fork) cudaEventDestroy(ev_fork);
@@ -295,7 +303,8 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 	}
 	CU(c->sample_out.alloc(n));
 	CU(c->hitrec.alloc(n));
-	if (c->sort_queues && c->prm.sampling == MCPT_SAMPLING_REFERENCE && n < (size_t(1) << 31)) {
+	if (c->sort_queues && n < (size_t(1) << 31)) {
+		if (c->prm.sampling != MCPT_SAMPLING_REFERENCE) { CU(c->mis_skeys.alloc(n)); CU(c->mis_sperm.alloc(n)); }
 		CU(c->sort_keys.alloc(n));
 		CU(c->sort_keys_out.alloc(n));
 		CU(c->sort_iota.alloc(n));
@@ -342,6 +351,13 @@ int reset_accumulation(mcpt_ctx* c) {
 // One wave of the fused pipeline: nsamples consecutive samples of every pixel.
 int ensure_wide(mcpt_ctx* c);
 
+// New scene or camera: the sort trial of the NEE + MIS mode starts over.  A trial still in flight is simply dropped
+// (its events are re-recorded by the next one).
+void reset_sort_trials(mcpt_ctx* c) {
+	for (auto& t : c->mis_trial) { t.pending = false; t.have = false; }
+	c->mis_sort_choice = -1;
+}
+
 // Folds the live counts of finished earlier waves into the per-bounce estimates (never waits).
 void poll_live_counts(mcpt_ctx* c) {
 	const int D = c->prm.max_depth;
@@ -352,6 +368,25 @@ void poll_live_counts(mcpt_ctx* c) {
 		for (int d = 0; d <= D; ++d) c->live_frac[size_t(d)] = double(h[d]) / double(c->slot_total[s]);
 	}
 	(void)cudaGetLastError();       // cudaErrorNotReady from the query is not an error
+}
+
+// This wave's live counts, for the sort sizes of later waves.  A slot is reused two waves later; by then its copy has
+// long completed unless the host runs more than a wave ahead, in which case it waits here (never for the wave it has
+// just enqueued).
+int record_live_counts(mcpt_ctx* c, long total) {
+	const int D = c->prm.max_depth;
+	const int s = c->next_slot;
+	if (c->slot_pending[s]) {
+		CU(cudaEventSynchronize(c->ev_counts[s]));
+		poll_live_counts(c);
+	}
+	CU(cudaMemcpyAsync(c->h_counts + size_t(s) * (size_t(D) + 2), c->qcount.p, sizeof(uint32_t) * (size_t(D) + 1),
+	                   cudaMemcpyDeviceToHost, c->stream));
+	CU(cudaEventRecord(c->ev_counts[s], c->stream));
+	c->slot_pending[s] = true;
+	c->slot_total[s] = total;
+	c->next_slot = s ^ 1;
+	return MCPT_OK;
 }
 
 int enqueue_wave(mcpt_ctx* c, int nsamples) {
@@ -370,6 +405,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	const int BS = c->block;
 	const int g = blocks(total, BS);
 	unsigned long long* cnt = c->counters.p;
+	uint32_t perm_n = 0;             // how many entries the sort behind the current permutation covered
 	for (int d = 0; d < D; ++d) {
 		bool timed = false;
 		if (c->time_bounces) {
@@ -394,6 +430,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 				k_wave_bounce_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, D, c->prm.tmin, c->prm.seed_mode, c->qhead.p + d);
 			} else {
 				w.perm = (sorted && d > 0) ? c->sort_perm.p : nullptr;       // primary rays are coherent as generated
+				w.perm_n = perm_n;
 				w.sort_keys = (sorted && d + 1 < D) ? c->sort_keys.p : nullptr;
 				k_wave_trace_persistent<<<std::min(g, c->persistent_grid(BS)), BS, 0, c->stream>>>(c->scene, w, d, c->prm.tmin, c->qhead.p + d);
 				if (c->time_bounces) {      // the timed kernel is the walk; the shader runs after the stop event
@@ -410,6 +447,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 					if (n_est > total) n_est = total;
 					CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->sort_keys.p, c->sort_keys_out.p,
 					                                   c->sort_iota.p, c->sort_perm.p, int(n_est), 0, SORT_KEY_BITS, c->stream));
+					perm_n = uint32_t(n_est);
 					c->launches += 6;       // invalidate + CUB's histogram, exclusive sum and 3 onesweep passes
 				}
 			}
@@ -423,22 +461,8 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	}
 	k_wave_resolve<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, nsamples, D, c->prm.max_attempt);
 	c->launches += uint64_t(D) + 2;
-	if (sorted) {
-		// this wave's live counts, for the sort sizes of later waves.  A slot is reused two waves later; by then its copy
-		// has long completed unless the host runs more than a wave ahead, in which case it waits here (never for the
-		// wave it has just enqueued).
-		const int s = c->next_slot;
-		if (c->slot_pending[s]) {
-			CU(cudaEventSynchronize(c->ev_counts[s]));
-			poll_live_counts(c);
-		}
-		CU(cudaMemcpyAsync(c->h_counts + size_t(s) * (size_t(D) + 2), c->qcount.p, sizeof(uint32_t) * (size_t(D) + 1),
-		                   cudaMemcpyDeviceToHost, c->stream));
-		CU(cudaEventRecord(c->ev_counts[s], c->stream));
-		c->slot_pending[s] = true;
-		c->slot_total[s] = total;
-		c->next_slot = s ^ 1;
-	}
+	if (sorted)
+		if (int r = record_live_counts(c, total)) return r;
 	CU(cudaGetLastError());
 	return MCPT_OK;
 }
@@ -601,13 +625,78 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 	const int BS = 128;
 	const int pg = std::min(blocks(total, BS), c->persistent_grid(BS));
 	const int sg = std::min(blocks(total, 256), c->nsm * 8);
+	// coherence-sorted queues as in enqueue_wave: the main queue of the next bounce and this bounce's shadow-ray queue
+	const bool sorted = c->sort_queues && c->sort_keys.p && c->mis_skeys.p && size_t(total) <= c->sort_keys.n && total >= (1L << 18);
+	if (sorted) poll_live_counts(c);
+	// the arrangement of this wave: the decided one; while undecided, one timed wave with both sorts, then one without
+	int mask = c->mis_sort_mask, trial = -1;
+	if (sorted && c->mis_sort_tune) {
+		if (c->mis_sort_choice < 0) {
+			for (auto& t : c->mis_trial) {
+				if (!t.pending || cudaEventQuery(t.t1) != cudaSuccess) continue;
+				float ms = 0.0f;
+				CU(cudaEventElapsedTime(&ms, t.t0, t.t1));
+				t.pending = false; t.have = true; t.ms_per_path = double(ms) / t.ms_per_path;
+			}
+			(void)cudaGetLastError();
+			if (c->mis_trial[0].have && c->mis_trial[1].have) c->mis_sort_choice = c->mis_trial[0].ms_per_path <= c->mis_trial[1].ms_per_path ? 3 : 0;
+		}
+		if (c->mis_sort_choice >= 0) mask = c->mis_sort_choice;
+		else if (c->live_frac[1] < 1.0) {         // live counts known: the sorts run at their steady-state sizes
+			for (int k = 0; k < 2 && trial < 0; ++k)
+				if (!c->mis_trial[k].have && !c->mis_trial[k].pending) trial = k;
+			if (trial >= 0) {
+				auto& t = c->mis_trial[trial];
+				if (!t.t0) { CU(cudaEventCreate(&t.t0)); CU(cudaEventCreate(&t.t1)); }
+				mask = trial == 0 ? 3 : 0;
+				CU(cudaEventRecord(t.t0, c->stream));
+			}
+		}
+	}
+	auto estimate = [&](int d) {      // live paths entering bounce d, from the previous waves (+2 % and a constant; the walk copes with more)
+		long n = long(c->live_frac[size_t(d)] * 1.02 * double(total)) + 4096;
+		return n > total ? total : n;
+	};
+	uint32_t perm_n = 0;
 	for (int d = 0; d < D; ++d) {
-		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, w.od[d & 1], w.dp[d & 1], w.hitrec, c->qcount.p + d, c->prm.tmin, c->qhead.p + d);
+		const bool sort_main = sorted && (mask & 1), sort_shadow = sorted && (mask & 2);
+		const uint32_t* perm = (sort_main && d > 0) ? c->sort_perm.p : nullptr;
+		m.keys = (sort_main && d + 1 < D) ? c->sort_keys.p : nullptr;
+		m.skeys = sort_shadow ? c->mis_skeys.p : nullptr;
+		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, w.od[d & 1], w.dp[d & 1], w.hitrec, c->qcount.p + d, c->prm.tmin, c->qhead.p + d, perm, perm_n);
+		const long ns = sorted ? estimate(d) : 0;          // shadow rays of bounce d: at most one per live path
+		if (sort_shadow) {       // the sorted prefix of the shadow queue starts invalid; live rays overwrite theirs; the main queue's
+			// invalid tail is maintained bounce by bounce like in the reference mode (k_invalidate_keys)
+			CU(cudaMemsetAsync(c->mis_skeys.p, 0xFF, sizeof(uint32_t) * size_t(ns), c->stream));
+		}
 		k_wave_shade_mis<<<sg, 256, 0, c->stream>>>(c->scene, w, m, d, D);
-		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, m.sod, m.sdp, m.shit, c->mis_scount.p + d, c->prm.tmin, c->mis_shead.p + d);
+		const uint32_t* sperm = nullptr;
+		if (sorted) {
+			if (sort_shadow) {
+				CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->mis_skeys.p, c->sort_keys_out.p, c->sort_iota.p,
+				                                   c->mis_sperm.p, int(ns), 0, SORT_KEY_BITS, c->stream));
+				sperm = c->mis_sperm.p;
+			}
+			if (m.keys) {
+				k_invalidate_keys<<<c->nsm * 2, 256, 0, c->stream>>>(c->sort_keys.p, c->qcount.p + d + 1, c->qcount.p + d);
+				CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->sort_keys.p, c->sort_keys_out.p, c->sort_iota.p,
+				                                   c->sort_perm.p, int(estimate(d + 1)), 0, SORT_KEY_BITS, c->stream));
+				perm_n = uint32_t(estimate(d + 1));
+			}
+			c->launches += 12;
+		}
+		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, m.sod, m.sdp, m.shit, c->mis_scount.p + d, c->prm.tmin, c->mis_shead.p + d, sperm, uint32_t(ns));
 		k_wave_nee_add<<<sg, 256, 0, c->stream>>>(m, d);
 	}
 	k_wave_resolve_mis<<<blocks(c->npix, 256), 256, 0, c->stream>>>(w, m, nsamples, D);
+	if (trial >= 0) {
+		auto& t = c->mis_trial[trial];
+		CU(cudaEventRecord(t.t1, c->stream));
+		t.pending = true;
+		t.ms_per_path = double(total);       // divisor until the time arrives
+	}
+	if (sorted)
+		if (int r = record_live_counts(c, total)) return r;
 	c->launches += uint64_t(4 * D) + 2;
 	CU(cudaGetLastError());
 	return MCPT_OK;
@@ -681,7 +770,7 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	c->nsm = prop.multiProcessorCount;
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
 	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128) c->block = b; }
-	if (const char* e = std::getenv("MCPT_SORT")) c->sort_queues = std::atoi(e) != 0;      // development A/B
+	if (const char* e = std::getenv("MCPT_SORT")) { c->sort_queues = std::atoi(e) != 0; if (c->sort_queues) c->mis_sort_mask = std::atoi(e) & 3; c->mis_sort_tune = false; }      // development A/B
 	if (const char* e = std::getenv("MCPT_HOST_TREE")) c->host_tree = std::atoi(e) != 0;
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;
@@ -1065,6 +1154,8 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
                         const mcpt_bvh_node* nodes, int nnodes, uint64_t tag, const void* blob, size_t blob_bytes) {
 	if (int r = check_ctx(c, false, false)) return r;
 	if (int r = check_scene_args(tris, ntris, mats, nmats, nodes, nnodes)) return r;
+	std::fill(c->live_frac.begin(), c->live_frac.end(), 1.0);     // sort sizes of the bounce queues: unknown again for new inputs
+	reset_sort_trials(c);
 	// ---- a layout derived earlier (scene cache): validated against these very arrays before anything else, never trusted
 	std::shared_ptr<DerivedScene> from_blob;
 	if (blob) {
@@ -1194,6 +1285,8 @@ static int upload_scene(mcpt_ctx* c, const mcpt_triangle* tris, int ntris, const
 int mcpt_set_camera(mcpt_ctx* c, const mcpt_camera* cam) {
 	if (int r = check_ctx(c, false, false)) return r;
 	if (!cam) return fail(MCPT_ERR_ARG, "mcpt_set_camera: null camera");
+	std::fill(c->live_frac.begin(), c->live_frac.end(), 1.0);
+	reset_sort_trials(c);
 	CameraDev d{};
 	d.center = f4{cam->center.x, cam->center.y, cam->center.z, cam->center.w};
 	d.direction = f4{cam->direction.x, cam->direction.y, cam->direction.z, cam->direction.w};
@@ -1633,6 +1726,16 @@ int mcpt_reset_stats(mcpt_ctx* c) {
 	CU(cudaStreamSynchronize(c->stream));
 	c->launches = 0;
 	c->stage_paths = 0;
+	return MCPT_OK;
+}
+
+int mcpt_get_queue_sorting(mcpt_ctx* c, int* out) {
+	if (int r = check_ctx(c, false, false)) return r;
+	if (!out) return fail(MCPT_ERR_ARG, "mcpt_get_queue_sorting: null output");
+	if (!c->sort_queues) *out = 0;
+	else if (c->prm.sampling == MCPT_SAMPLING_REFERENCE) *out = 1;
+	else if (!c->mis_sort_tune) *out = c->mis_sort_mask;
+	else *out = c->mis_sort_choice;
 	return MCPT_OK;
 }
 

@@ -164,6 +164,8 @@ struct WaveDev {
 	uint32_t* seeds;        // per-pixel persistent LCG state (seed_mode 0)
 	uint32_t* sort_keys;    // coherence key of queue item i of the NEXT bounce, written by the shade kernel (null: queues stay unsorted)
 	const uint32_t* perm;   // walk order of THIS bounce's queue: the walk kernel's i-th ray is item perm[i] (null: identity)
+	uint32_t perm_n;        // entries of perm that were sorted (an estimate of the live count made on the host): they are a
+	                        // permutation of [0, perm_n) whenever the queue is longer, so items from perm_n on walk in queue order
 	uint32_t capacity;      // items every queue buffer holds (checked build: bound of queue positions and path ids)
 	float4* hist;
 	int32_t* counts;
@@ -513,7 +515,7 @@ struct TraceJob {
 	int src;
 	unsigned total;         // items in this bounce's queue (bound of the permutation's entries in the checked build)
 	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
-		if (w.perm) item = __ldcs(w.perm + item);       // walk order -> queue position; finish() writes the record there
+		if (w.perm && item < w.perm_n) item = __ldcs(w.perm + item);   // walk order -> queue position; finish() writes the record there
 		MCPT_CHECK_INDEX(CHK_PERM, item, total);
 		const unsigned i = item;
 		const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i);

@@ -42,6 +42,8 @@ struct MisDev {
 	float4* sod;            // shadow rays of the current bounce: origin
 	float4* sdp;            //   direction + path id
 	float4* scon;           //   contribution if unoccluded (rgb) + sampled emitter triangle
+	uint32_t* keys;         // coherence keys of the NEXT bounce's queue items (null: queues stay unsorted), as in WaveDev
+	uint32_t* skeys;        //   ... and of this bounce's shadow rays
 	float* den;             // ratio mode, per path: estimate of P(X != 0) so far (null in MCPT_SAMPLING_NEE_MIS)
 	float* sden;            // ratio mode, per shadow ray: its share of that estimate if unoccluded
 	float2* shit;           //   hit record written by the walk
@@ -57,7 +59,11 @@ struct QueueTraceJob {
 	const float4* od;
 	const float4* dp;
 	float2* hitrec;
-	__device__ __forceinline__ bool load(unsigned i, RayRegs& ray) {
+	const uint32_t* perm;   // walk order (coherence-sorted queue) or null
+	uint32_t perm_n;        // sorted entries (WaveDev::perm_n)
+	__device__ __forceinline__ bool load(unsigned& item, RayRegs& ray) {
+		if (perm && item < perm_n) item = __ldcs(perm + item);
+		const unsigned i = item;
 		const float4 o = __ldcs(od + i), d = __ldcs(dp + i);
 		ray.origin = ld4(o);
 		ray.direction = f4{d.x, d.y, d.z, 0.0f};
@@ -69,8 +75,8 @@ struct QueueTraceJob {
 };
 
 __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_trace_queue_persistent(SceneDev sc, const float4* od, const float4* dp, float2* hitrec,
-                                                                const uint32_t* count, float tmin, unsigned* head) {
-	QueueTraceJob job{od, dp, hitrec};
+                                                                const uint32_t* count, float tmin, unsigned* head, const uint32_t* perm, uint32_t perm_n) {
+	QueueTraceJob job{od, dp, hitrec, perm, perm_n};
 	persistent_walk(sc, tmin, *count, head, job);
 }
 
@@ -205,6 +211,7 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
 				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
 				__stcs(m.pdf[dst] + pos, pdf_next);
+				if (m.keys) m.keys[pos] = ray_sort_key(sc, ray);
 			}
 		}
 		mask = __ballot_sync(0xffffffffu, shadow);
@@ -218,6 +225,12 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 				__stcs(m.sdp + pos, s_d);
 				__stcs(m.scon + pos, s_c);
 				if (m.sden) __stcs(m.sden + pos, s_den);
+				if (m.skeys) {
+					RayRegs sr;
+					sr.origin = f4{s_o.x, s_o.y, s_o.z, 0.0f};
+					sr.direction = f4{s_d.x, s_d.y, s_d.z, 0.0f};
+					m.skeys[pos] = ray_sort_key(sc, sr);
+				}
 			}
 		}
 	}

@@ -26,7 +26,7 @@ EXPORTS = [
     "mcpt_reset_accumulation", "mcpt_read_rays", "mcpt_write_rays", "mcpt_read_hits", "mcpt_write_hits",
     "mcpt_read_color", "mcpt_write_color", "mcpt_read_seeds", "mcpt_write_seeds", "mcpt_read_history",
     "mcpt_read_sums", "mcpt_bind_sums", "mcpt_trace", "mcpt_trace_device", "mcpt_trace_count", "mcpt_get_stats",
-    "mcpt_reset_stats", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
+    "mcpt_reset_stats", "mcpt_get_queue_sorting", "mcpt_set_profiling", "mcpt_get_bounce_time", "mcpt_build_lbvh",
     "mcpt_optimize_treelet", "mcpt_measure_read_bandwidth", "mcpt_bvh_metrics", "mcpt_merge_sums",
     "mcpt_upload_scene_tagged", "mcpt_write_sums", "mcpt_write_history", "mcpt_get_first_sample",
     "mcpt_trace_noalloc", "mcpt_derive_scene", "mcpt_free_blob", "mcpt_upload_scene_derived", "mcpt_phong_accept_table", "mcpt_check_failures", "mcpt_derive_scene_device",
@@ -315,6 +315,12 @@ class Context:
 
     def reset_stats(self):
         self._call("mcpt_reset_stats")
+
+    def queue_sorting(self):
+        """bit 0: path queue sorted, bit 1: shadow-ray queue sorted; -1 while the NEE + MIS modes are still timing both."""
+        v = ctypes.c_int(0)
+        self._call("mcpt_get_queue_sorting", ctypes.byref(v))
+        return v.value
 
 
 def image_from_sums(sums, width, height):

@@ -180,3 +180,27 @@ def test_upload_with_a_cached_layout_equals_a_fresh_upload(cbox, mis):
         b.reset_accumulation()
         b.render(6)
         assert b.read_sums().tobytes() == sums_a.tobytes()
+
+
+def test_sort_sizes_estimated_from_an_earlier_camera_do_not_lose_rays(cbox):
+    """The bounce queues are sorted over an ESTIMATE of their live length taken from earlier waves.  After a camera that
+    sees nothing (every path dies at once) the estimates are far too small for the real camera: items beyond the sorted
+    prefix must then walk in queue order - same sums as a context that never saw the first camera."""
+    w = h = 512
+    kw = dict(max_depth=8, max_attempt=1 << 20, seed_mode=1, run_seed=9, samples_in_flight=2)
+    away = cbox.camera.copy()
+    away["direction"][0][:3] = -away["direction"][0][:3]          # looking away from the box
+    with _ctx(cbox, w, h, **kw) as a:
+        a.set_camera(away)
+        a.render(6)                                               # three waves: their (empty) live counts are polled
+        assert a.read_sums()[6].sum() == 0
+        a.set_camera(cbox.camera)
+        a.reset_accumulation()
+        a.render(4)
+        got = a.read_sums()
+        rays = a.stats()["rays_traced"]
+    with _ctx(cbox, w, h, **kw) as b:
+        b.render(4)
+        want = b.read_sums()
+    assert got.tobytes() == want.tobytes() and want[6].sum() > 0
+    assert rays > 6 * w * h

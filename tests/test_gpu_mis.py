@@ -135,3 +135,31 @@ def test_image_agrees_with_a_long_reference_render(name, mode, w, h, depth, log_
     rel_r = np.sqrt(var_r).mean(0) / np.maximum(img_r.mean(0), 1e-30) * np.sqrt(spp_ref / float(_BATCHES << log_mis))
     gain = np.median(rel_r[ok] / np.maximum(rel_m[ok], 1e-30))
     assert gain > (4.0 if mode == device.SAMPLING_NEE_MIS_RATIO else 2.0), gain
+
+
+@pytest.mark.parametrize("mode", [device.SAMPLING_NEE_MIS, device.SAMPLING_NEE_MIS_RATIO])
+def test_queue_sorting_and_its_self_tuning_do_not_change_the_image(mode, cbox, monkeypatch):
+    """The main and the shadow queues are walked in coherence-sorted order, and the library times one wave sorted and
+    one unsorted before it settles on an arrangement: every arrangement must accumulate the same bits."""
+    w = h = 512                              # 2 samples in flight = 2^19 paths per wave: above the sorting threshold
+
+    def run(sort_env):
+        if sort_env is None:
+            monkeypatch.delenv("MCPT_SORT", raising=False)
+        else:
+            monkeypatch.setenv("MCPT_SORT", sort_env)
+        with device.Context(w, h, DEPTH, 1 << 30, seed_mode=1, run_seed=5, sampling=mode, samples_in_flight=2) as ctx:
+            ctx.upload_scene(cbox.triangles, cbox.materials, cbox.nodes)
+            ctx.set_camera(cbox.camera)
+            seen = []
+            for _ in range(6):               # wave 1 learns the live counts, 2 timed trial waves, then the settled choice
+                ctx.render(2)
+                seen.append(ctx.queue_sorting())
+            return ctx.read_sums().tobytes(), seen
+
+    tuned, seen = run(None)
+    assert seen[0] == -1 and seen[-1] in (0, 3), seen
+    for pinned in ("0", "1", "2", "3"):
+        got, seen = run(pinned)
+        assert seen == [int(pinned)] * 6
+        assert got == tuned, pinned
