@@ -40,42 +40,35 @@ __device__ __forceinline__ f4 operator-(f4 a, f4 b) { return {a.x - b.x, a.y - b
 __device__ __forceinline__ f4 operator*(f4 a, f4 b) { return {a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w}; }
 __device__ __forceinline__ f4 operator*(float s, f4 a) { return {s * a.x, s * a.y, s * a.z, s * a.w}; }
 __device__ __forceinline__ f4 operator*(f4 a, float s) { return {a.x * s, a.y * s, a.z * s, a.w * s}; }
+// The shader's vector divisions (normalisations: three per randomDirection) through one double-precision reciprocal:
+// x = a / s of two floats is either a float itself or further than 2^-49 (relative) from every float and every midpoint
+// between floats (a - m s is a non-zero multiple of the last bit of the 49-bit product m s), and double(a) * RN(1 / double(s))
+// is within 2^-51.9 of x, so narrowing it rounds like the IEEE quotient - for every finite a and s, denormal results
+// included (their grid is coarser) - without the divider's subroutine and its slow path for small operands
+// (tools/src/div_two_pi_check.c enumerates the constant-divisor case and samples this one).
+#ifndef MCPT_DRCP_DIV
+#define MCPT_DRCP_DIV 1          // 0: the hardware divider (A/B: -0.3 % on the headline loop, profiles/r3m_ab_drcp_div.log)
+#endif
 __device__ __forceinline__ f4 operator/(f4 a, float s) {
-#if MCPT_FDIV_BYPASS & 2
+#if MCPT_DRCP_DIV & 1
+	const double r = __drcp_rn(double(s));
+	return {float(double(a.x) * r), float(double(a.y) * r), float(double(a.z) * r), float(double(a.w) * r)};
+#elif MCPT_FDIV_BYPASS & 2
 	return {fdiv(a.x, s), fdiv(a.y, s), fdiv(a.z, s), fdiv(a.w, s)};
-#elif MCPT_FDIV_BYPASS & 4
-	f4 r{a.x / s, a.y / s, a.z / s, a.w};                  // w lanes are zero almost everywhere: +-0 / positive = +-0
-	if (!(a.w == 0.0f && s > 0.0f)) r.w = a.w / s;
-	return r;
 #else
 	return {a.x / s, a.y / s, a.z / s, a.w / s};
 #endif
 }
 // Division of a path's throughput by 2 pi (shade.cl:120,143).  Throughputs shrink by ~2^-7 per bounce and the Phong
 // lobe's pow(cos, Ns = 4000) adds factors of 2^-100 at once: on the diningroom stand-in 5 % of the live rays carry a
-// channel below 2^-120 at bounce 8 and 13 % a denormal one at bounce 14 (tools/throughput_probe.py).  There the
-// hardware's division takes its slow path - a ~100-instruction subroutine the whole warp waits for while one or two
-// lanes run it: 22 % of k_wave_shade's warp instructions at a mid-depth bounce (ncu r2m).  Both detours below return
-// the correctly rounded float quotient, i.e. the same bits as `a / b`:
-//  * 2^-120 <= |a| < 2^-40: ((a * 2^64) / b) * 2^-64.  Scaling by a power of two commutes with round-to-nearest while
-//    nothing leaves the normal range (|a / b| >= 2^-123 for b = 2 pi, so the last product is exact).
-//  * 0 < |a| < 2^-120 (quotient possibly denormal): float(double(a) / double(b)).  A quotient of two 24-bit numbers that
-//    is not itself a rounding midpoint of the (at most 24-bit) target lies at least 2^-49 (relative) away from every
-//    midpoint, the 53-bit division moves it by at most 2^-53, so the second rounding decides as a single one would; the
-//    conversion rounds into the denormal range correctly (-ftz=false).
-#ifndef MCPT_SCALED_DIV
-#define MCPT_SCALED_DIV 1       // bit 0: power-of-two scaling (+0.4 % on the headline loop); bit 1: double-precision detour for the
-                                // smallest operands (bit-exact too, but -0.9 %: the extra branch costs more than the subroutine it avoids; off)
-#endif
+// channel below 2^-120 at bounce 8 and 13 % a denormal one at bounce 14 (tools/throughput_probe.py), where the hardware's
+// divider takes its slow path - a ~100-instruction subroutine the whole warp waits for while one or two lanes run it
+// (19 % of k_wave_shade's warp instructions at a mid-depth bounce, ncu r3i).  The divisor is a constant, so:
+// float(double(a) * RN(1 / double(2 pi))) carries the bits of a / (float)(2 pi) for EVERY float a - enumerated over all
+// 2^32 of them (tools/src/div_two_pi_check.c, tests/test_div_two_pi.py).  Three instructions, no slow path.
 __device__ __forceinline__ float fdiv_two_pi(float a) {
-	const float aa = fabsf(a);
-#if MCPT_SCALED_DIV & 2
-	if (aa < 0x1p-120f && aa > 0.0f) return float(double(a) / double(TWO_PI_F));
-#endif
-#if MCPT_SCALED_DIV & 1
-	const bool tiny = aa < 0x1p-40f && aa >= 0x1p-120f;
-	const float up = tiny ? 0x1p64f : 1.0f, down = tiny ? 0x1p-64f : 1.0f;
-	return fdiv(a * up, TWO_PI_F) * down;
+#if MCPT_DRCP_DIV & 1
+	return float(double(a) * 0x1.45f306446f9b4p-3);
 #else
 	return fdiv(a, TWO_PI_F);
 #endif

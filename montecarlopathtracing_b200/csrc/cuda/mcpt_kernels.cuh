@@ -167,6 +167,9 @@ struct WaveDev {
 	uint32_t perm_n;        // entries of perm that were sorted (an estimate of the live count made on the host): they are a
 	                        // permutation of [0, perm_n) whenever the queue is longer, so items from perm_n on walk in queue order
 	uint32_t capacity;      // items every queue buffer holds (checked build: bound of queue positions and path ids)
+	float4* pow_req;        // deferred Phong pows of this bounce: (queue position of the next bounce, base, exponent, trailing factor);
+	uint32_t* pow_count;    //   null: k_wave_shade evaluates them in place.  pow_count = this bounce's request counter
+	uint32_t pow_capacity;  //   requests pow_req holds; a bounce with more evaluates the rest in place
 	float4* hist;
 	int32_t* counts;
 	double* sums;
@@ -350,14 +353,6 @@ namespace mcpt {
 #ifndef MCPT_MIN_BLOCKS
 #define MCPT_MIN_BLOCKS 8        // resident 128-thread blocks per SM the persistent kernels are compiled for (8 -> 64 registers)
 #endif
-#ifndef MCPT_SHADE_BINS
-#define MCPT_SHADE_BINS 0        // 8: direction-octant grouping of the next queue inside each shading block - measured -1.6% (the origins stay incoherent)
-#endif
-#ifndef MCPT_DENSE_POW
-#define MCPT_DENSE_POW 0         // 1: k_wave_shade gathers the block's Phong pows and evaluates them in full warps.
-                                 // Bit-identical; measured -1.5% on the loop (three block barriers per batch cost
-                                 // more than the pow's 27% of instructions at 2-4 lanes save), so it is off.
-#endif
 #ifndef MCPT_REFILL_THRESHOLD
 #define MCPT_REFILL_THRESHOLD 16       // lanes still walking below which a warp refills; with coherence-sorted queues 16 measured +0.6 % over 22 (26: -0.4 %, 30: -0.9 %; profiles/r2l_ab_walk_variants.log)
 #endif
@@ -539,13 +534,6 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 	const uint32_t total = w.qcount[depth];
 	const unsigned lane = threadIdx.x & 31u;
 	const uint32_t stride = gridDim.x * blockDim.x;
-#if MCPT_SHADE_BINS
-	__shared__ uint32_t bin_count[MCPT_SHADE_BINS], bin_base[MCPT_SHADE_BINS];
-#endif
-#if MCPT_DENSE_POW
-	__shared__ float pow_x[256], pow_y[256];
-	__shared__ uint32_t pow_count;
-#endif
 	for (uint32_t bbase = blockIdx.x * blockDim.x; bbase < total; bbase += stride) {   // block-uniform trip count
 		const uint32_t i = bbase + threadIdx.x;
 		bool alive = false, finished = false;
@@ -553,9 +541,7 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 		f4 color{0, 0, 0, 0};
 		uint32_t seed = 0;
 		int path = 0;
-#if MCPT_DENSE_POW
 		PhongDefer defer{0.0f, 0.0f, 0.0f, false};
-#endif
 		if (i < total) {
 			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
 			const float2 hr = __ldcs(w.hitrec + i);
@@ -578,75 +564,55 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 				ip = ray.origin + t * ray.direction;
 				if (dot3(ray.direction, nn) > 0) nn = -nn;
 			}
-#if MCPT_DENSE_POW
-			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, nullptr, &defer);
-#else
-			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth);
-#endif
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, nullptr, w.pow_req ? &defer : nullptr);
 			finished = !alive;
 		}
-#if MCPT_DENSE_POW
-		// the block's Phong pows, gathered and evaluated by full warps (see PhongDefer)
-		if (threadIdx.x == 0) pow_count = 0u;
-		__syncthreads();
-		uint32_t slot = 0;
-		if (defer.pending) {
-			slot = atomicAdd(&pow_count, 1u);
-			pow_x[slot] = defer.x;
-			pow_y[slot] = defer.y;
-		}
-		__syncthreads();
-		if (threadIdx.x < pow_count) pow_x[threadIdx.x] = cr_pow(pow_x[threadIdx.x], pow_y[threadIdx.x]);
-		__syncthreads();
-		if (defer.pending) finish_phong(color, pow_x[slot], defer.post);
-#endif
 		if (finished) {
 			__stcs(w.sample_out + path, make_float4(color.x, color.y, color.z, 0.0f));
 			if (seed_mode == 0) w.seeds[path % w.npix] = seed;
 		}
-#if MCPT_SHADE_BINS
-		// The block's survivors enter the next queue grouped by direction octant (a counting sort in shared
-		// memory), so that the 32 consecutive rays a walking warp fetches mostly point the same way: they
-		// share nodes (fewer L1 wavefronts) and take similar turns.  Queue order is free - results do not
-		// depend on it.
-		if (threadIdx.x < MCPT_SHADE_BINS) bin_count[threadIdx.x] = 0u;
-		__syncthreads();
-		uint32_t bin = 0, rank = 0;
-		if (alive) {
-			bin = (ray.direction.x < 0.0f ? 1u : 0u) | (ray.direction.y < 0.0f ? 2u : 0u) | (ray.direction.z < 0.0f ? 4u : 0u);
-			rank = atomicAdd(&bin_count[bin], 1u);
-		}
-		__syncthreads();
-		if (threadIdx.x == 0) {
-			uint32_t sum = 0;
-			for (int b = 0; b < MCPT_SHADE_BINS; ++b) sum += bin_count[b];
-			uint32_t qb = sum ? atomicAdd(&w.qcount[depth + 1], sum) : 0u;
-			for (int b = 0; b < MCPT_SHADE_BINS; ++b) { bin_base[b] = qb; qb += bin_count[b]; }
-		}
-		__syncthreads();
-		if (alive) {
-			const uint32_t pos = bin_base[bin] + rank;
-			__stcs(w.od[dst] + pos, st4(ray.origin));
-			__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
-			__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
-		}
-		__syncthreads();
-#else
 		const unsigned mask = __ballot_sync(0xffffffffu, alive);
 		if (mask) {
 			uint32_t qb = 0;
 			if (lane == 0) qb = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(mask)));
 			qb = __shfl_sync(0xffffffffu, qb, 0);
+			// The Phong lobe's pow is a double-precision subroutine that 2 of a warp's 32 lanes need (ncu r3i: 32 % of this
+			// kernel's warp instructions): the lanes leave colour * ks in the queue and a request behind, and k_wave_pow
+			// finishes them in full warps - same operations in the same order (finish_phong).
+			const unsigned pmask = __ballot_sync(0xffffffffu, defer.pending);
+			uint32_t pb = 0;
+			if (pmask) {
+				if (lane == 0) pb = atomicAdd(w.pow_count, uint32_t(__popc(pmask)));
+				pb = __shfl_sync(0xffffffffu, pb, 0);
+			}
 			if (alive) {
 				uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
 				MCPT_CHECK_INDEX(CHK_QUEUE, pos, w.capacity);
+				if (defer.pending) {
+					const uint32_t slot = pb + uint32_t(__popc(pmask & ((1u << lane) - 1u)));
+					if (slot < w.pow_capacity) __stcs(w.pow_req + slot, make_float4(__int_as_float(int(pos)), defer.x, defer.y, defer.post));
+					else finish_phong(color, cr_pow(defer.x, defer.y), defer.post);
+				}
 				__stcs(w.od[dst] + pos, st4(ray.origin));
 				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
 				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
 				if (w.sort_keys) w.sort_keys[pos] = ray_sort_key(sc, ray);
 			}
 		}
-#endif
+	}
+}
+
+// The deferred Phong pows of a bounce (see k_wave_shade), one per thread.
+__global__ void __launch_bounds__(256) k_wave_pow(WaveDev w, int dst) {
+	const uint32_t n = min(*w.pow_count, w.pow_capacity);
+	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+		const float4 r = __ldcs(w.pow_req + i);
+		const uint32_t pos = uint32_t(__float_as_int(r.x));
+		MCPT_CHECK_INDEX(CHK_QUEUE, pos, w.capacity);
+		const float4 c = w.cs[dst][pos];
+		f4 color{c.x, c.y, c.z, 0.0f};
+		finish_phong(color, cr_pow(r.y, r.z), r.w);
+		w.cs[dst][pos] = make_float4(color.x, color.y, color.z, c.w);
 	}
 }
 
