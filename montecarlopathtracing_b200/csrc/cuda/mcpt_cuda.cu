@@ -161,8 +161,6 @@ struct mcpt_ctx {
 	int wave_samples = 0;             // allocated samples per wave
 	DevBuf<float4> od[2], dp[2], cs[2], sample_out;
 	DevBuf<float2> hitrec;
-	DevBuf<float4> pow_req;                // deferred Phong pows of one bounce (k_wave_shade -> k_wave_pow)
-	DevBuf<uint32_t> pow_count;            // per bounce
 	// NEE + MIS mode
 	DevBuf<float4> mis_rad, mis_sod, mis_sdp, mis_scon;
 	DevBuf<float> mis_pdf[2], emit_cdf, phong_accept, mis_den, mis_sden;
@@ -305,10 +303,6 @@ int ensure_wave(mcpt_ctx* c, int samples) {
 	}
 	CU(c->sample_out.alloc(n));
 	CU(c->hitrec.alloc(n));
-	if (!(c->opt_flags & 128)) {       // MCPT_OPT bit 7: pows evaluated in place (A/B)
-		CU(c->pow_req.alloc(n / 4 + 1024));      // glossy hits take the Phong lobe with probability 1/2; a bounce with more requests finishes the rest in place
-		CU(c->pow_count.alloc(size_t(c->prm.max_depth) + 2));
-	}
 	if (c->sort_queues && n < (size_t(1) << 31)) {
 		if (c->prm.sampling != MCPT_SAMPLING_REFERENCE) { CU(c->mis_skeys.alloc(n)); CU(c->mis_sperm.alloc(n)); }
 		CU(c->sort_keys.alloc(n));
@@ -405,8 +399,6 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 	if (sorted) poll_live_counts(c);
 	CU(cudaMemsetAsync(c->qcount.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	CU(cudaMemsetAsync(c->qhead.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
-	const bool defer_pow = c->pow_req.p != nullptr;
-	if (defer_pow) CU(cudaMemsetAsync(c->pow_count.p, 0, sizeof(uint32_t) * (D + 2), c->stream));
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int trav = c->traversal(c->prm.traversal);
 	if (trav == MCPT_TRAVERSAL_WIDE8) if (int r = ensure_wide(c)) return r;
@@ -446,17 +438,8 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 					c->ev_used += 2;
 					timed = true;
 				}
-				if (defer_pow && d + 1 < D) {       // (the last bounce ends every path: nothing to finish)
-					w.pow_req = c->pow_req.p;
-					w.pow_count = c->pow_count.p + d;
-					w.pow_capacity = uint32_t(std::min<size_t>(c->pow_req.n, 0xffffffffu));
-				} else w.pow_req = nullptr;
 				k_wave_shade<<<std::min(blocks(total, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, d, D, c->prm.seed_mode);
 				++c->launches;
-				if (w.pow_req) {
-					k_wave_pow<<<c->nsm * 4, 256, 0, c->stream>>>(w, (d & 1) ^ 1);
-					++c->launches;
-				}
 				if (w.sort_keys) {
 					// the next bounce's walk order: live items first (their keys are fresh), sorted by coherence key
 					k_invalidate_keys<<<c->nsm * 2, 256, 0, c->stream>>>(c->sort_keys.p, c->qcount.p + d + 1, c->qcount.p + d);

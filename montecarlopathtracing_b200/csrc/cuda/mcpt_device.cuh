@@ -47,7 +47,9 @@ __device__ __forceinline__ f4 operator*(f4 a, float s) { return {a.x * s, a.y * 
 // included (their grid is coarser) - without the divider's subroutine and its slow path for small operands
 // (tools/src/div_two_pi_check.c enumerates the constant-divisor case and samples this one).
 #ifndef MCPT_DRCP_DIV
-#define MCPT_DRCP_DIV 1          // 0: the hardware divider (A/B: -0.3 % on the headline loop, profiles/r3m_ab_drcp_div.log)
+#define MCPT_DRCP_DIV 3          // bit 0: the normalisations, bit 1: the division by 2 pi; 0 = the hardware divider.  Mrays/s, 0 -> 3
+                                 // (profiles/r3q_scene_rates.log): diningroom 4 245 -> 4 366, its seed_mode 0 pixel chains 3 158 -> 3 610,
+                                 // cbox 4 651 -> 4 781, veach_mis 7 124 -> 6 852 (its shader is bound by the conversions' pipe)
 #endif
 __device__ __forceinline__ f4 operator/(f4 a, float s) {
 #if MCPT_DRCP_DIV & 1
@@ -67,7 +69,7 @@ __device__ __forceinline__ f4 operator/(f4 a, float s) {
 // float(double(a) * RN(1 / double(2 pi))) carries the bits of a / (float)(2 pi) for EVERY float a - enumerated over all
 // 2^32 of them (tools/src/div_two_pi_check.c, tests/test_div_two_pi.py).  Three instructions, no slow path.
 __device__ __forceinline__ float fdiv_two_pi(float a) {
-#if MCPT_DRCP_DIV & 1
+#if MCPT_DRCP_DIV & 2
 	return float(double(a) * 0x1.45f306446f9b4p-3);
 #else
 	return fdiv(a, TWO_PI_F);
@@ -246,21 +248,13 @@ __device__ __forceinline__ MaterialDev load_material(const mcpt_material* __rest
 	return m;
 }
 
-// The Phong lobe's pow (shade.cl:143) is a double-precision subroutine that a handful of lanes per warp need
-// (ncu r1n: 27% of the shade kernel's instructions at 2-4 of 32 lanes).  With `defer`, shade_one leaves that one
-// factor open: colour holds colour * ks, the arguments and the trailing factor go to *defer, and the caller finishes
-// with finish_phong() once it has evaluated the pows of a whole block in dense warps.  Same operations, same order.
-struct PhongDefer { float x, y, post; bool pending; };
-__device__ __forceinline__ void finish_phong(f4& color, float p, float post) { color = div_two_pi(color * p * post); }
-
 __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats, const float2* __restrict__ cs_table,
                                           RayRegs& ray, float hit_t, f4 n, f4 ip, uint32_t material_id, f4& color,
                                           uint32_t& seed_slot, int max_depth, bool* diffuse_lobe = nullptr,
-                                          PhongDefer* defer = nullptr, f4* phong_axis = nullptr) {
+                                          f4* phong_axis = nullptr) {
 	// phong_axis (NEE + MIS mode): receives the mirror direction with w = 1 when the glossy lobe was taken, else w = 0
 	if (phong_axis) *phong_axis = f4{0, 0, 0, 0};
 	if (diffuse_lobe) *diffuse_lobe = false;
-	if (defer) defer->pending = false;
 	const uint32_t state = uint32_t(__float_as_int(ray.origin.w));
 	if (hit_t >= FLT_MAX) {                                                   // :92-96
 		color = f4{0, 0, 0, 0};
@@ -284,10 +278,7 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		} while (specular && dot3(new_dir, n) <= 0);
 		new_org = ip + KERNEL_EPSILON * new_dir;
 		new_state = int32_t(state) + 1;
-		if (specular && defer) {
-			color = color * mat.ka_ks;
-			defer->x = dot3(new_dir, axis); defer->y = mat.Ns; defer->post = dot3(new_dir, n); defer->pending = true;
-		} else if (specular) color = div_two_pi(color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n));
+		if (specular) color = div_two_pi(color * mat.ka_ks * cr_pow(dot3(new_dir, axis), mat.Ns) * dot3(new_dir, n));
 		else color = div_two_pi(color * mat.kd * dot3(new_dir, n));
 		if (diffuse_lobe) *diffuse_lobe = !specular;
 		if (phong_axis && specular) *phong_axis = f4{axis.x, axis.y, axis.z, 1.0f};
@@ -327,7 +318,6 @@ __device__ __forceinline__ bool shade_one(const mcpt_material* __restrict__ mats
 		color = f4{0, 0, 0, 0};
 		new_state = int32_t(uint32_t(new_state) | MCPT_RAY_TERM_MASK);
 		alive = false;
-		if (defer) defer->pending = false;                                     // the colour is already final (zero)
 	}
 	const float pixel_w = ray.direction.w;
 	ray.origin = f4{new_org.x, new_org.y, new_org.z, __int_as_float(new_state)};

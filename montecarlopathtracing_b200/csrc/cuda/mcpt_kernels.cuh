@@ -167,9 +167,6 @@ struct WaveDev {
 	uint32_t perm_n;        // entries of perm that were sorted (an estimate of the live count made on the host): they are a
 	                        // permutation of [0, perm_n) whenever the queue is longer, so items from perm_n on walk in queue order
 	uint32_t capacity;      // items every queue buffer holds (checked build: bound of queue positions and path ids)
-	float4* pow_req;        // deferred Phong pows of this bounce: (queue position of the next bounce, base, exponent, trailing factor);
-	uint32_t* pow_count;    //   null: k_wave_shade evaluates them in place.  pow_count = this bounce's request counter
-	uint32_t pow_capacity;  //   requests pow_req holds; a bounce with more evaluates the rest in place
 	float4* hist;
 	int32_t* counts;
 	double* sums;
@@ -541,7 +538,6 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 		f4 color{0, 0, 0, 0};
 		uint32_t seed = 0;
 		int path = 0;
-		PhongDefer defer{0.0f, 0.0f, 0.0f, false};
 		if (i < total) {
 			const float4 o = __ldcs(w.od[src] + i), d = __ldcs(w.dp[src] + i), c = __ldcs(w.cs[src] + i);
 			const float2 hr = __ldcs(w.hitrec + i);
@@ -564,7 +560,7 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 				ip = ray.origin + t * ray.direction;
 				if (dot3(ray.direction, nn) > 0) nn = -nn;
 			}
-			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, nullptr, w.pow_req ? &defer : nullptr);
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth);
 			finished = !alive;
 		}
 		if (finished) {
@@ -576,43 +572,15 @@ __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int 
 			uint32_t qb = 0;
 			if (lane == 0) qb = atomicAdd(&w.qcount[depth + 1], uint32_t(__popc(mask)));
 			qb = __shfl_sync(0xffffffffu, qb, 0);
-			// The Phong lobe's pow is a double-precision subroutine that 2 of a warp's 32 lanes need (ncu r3i: 32 % of this
-			// kernel's warp instructions): the lanes leave colour * ks in the queue and a request behind, and k_wave_pow
-			// finishes them in full warps - same operations in the same order (finish_phong).
-			const unsigned pmask = __ballot_sync(0xffffffffu, defer.pending);
-			uint32_t pb = 0;
-			if (pmask) {
-				if (lane == 0) pb = atomicAdd(w.pow_count, uint32_t(__popc(pmask)));
-				pb = __shfl_sync(0xffffffffu, pb, 0);
-			}
 			if (alive) {
 				uint32_t pos = qb + uint32_t(__popc(mask & ((1u << lane) - 1u)));
 				MCPT_CHECK_INDEX(CHK_QUEUE, pos, w.capacity);
-				if (defer.pending) {
-					const uint32_t slot = pb + uint32_t(__popc(pmask & ((1u << lane) - 1u)));
-					if (slot < w.pow_capacity) __stcs(w.pow_req + slot, make_float4(__int_as_float(int(pos)), defer.x, defer.y, defer.post));
-					else finish_phong(color, cr_pow(defer.x, defer.y), defer.post);
-				}
 				__stcs(w.od[dst] + pos, st4(ray.origin));
 				__stcs(w.dp[dst] + pos, make_float4(ray.direction.x, ray.direction.y, ray.direction.z, __int_as_float(path)));
 				__stcs(w.cs[dst] + pos, make_float4(color.x, color.y, color.z, __int_as_float(int(seed))));
 				if (w.sort_keys) w.sort_keys[pos] = ray_sort_key(sc, ray);
 			}
 		}
-	}
-}
-
-// The deferred Phong pows of a bounce (see k_wave_shade), one per thread.
-__global__ void __launch_bounds__(256) k_wave_pow(WaveDev w, int dst) {
-	const uint32_t n = min(*w.pow_count, w.pow_capacity);
-	for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-		const float4 r = __ldcs(w.pow_req + i);
-		const uint32_t pos = uint32_t(__float_as_int(r.x));
-		MCPT_CHECK_INDEX(CHK_QUEUE, pos, w.capacity);
-		const float4 c = w.cs[dst][pos];
-		f4 color{c.x, c.y, c.z, 0.0f};
-		finish_phong(color, cr_pow(r.y, r.z), r.w);
-		w.cs[dst][pos] = make_float4(color.x, color.y, color.z, c.w);
 	}
 }
 

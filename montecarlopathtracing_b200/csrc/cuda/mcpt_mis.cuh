@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256) k_wave_shade_mis(SceneDev sc, WaveDev w, 
 			uint32_t nee_rng = seed ^ 0xA511E9B3u;            // before the chain advances the LCG
 			bool diffuse_lobe = false;
 			f4 phong_axis;
-			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, &diffuse_lobe, nullptr, &phong_axis);
+			alive = shade_one(sc.materials, sc.cs_table, ray, t, nn, ip, mat, color, seed, max_depth, &diffuse_lobe, &phong_axis);
 			const bool phong_lobe = phong_axis.w != 0.0f;
 			const float accept = phong_lobe ? phong_accept_probability(m.phong_accept, dot3(phong_axis, nn)) : 1.0f;
 			float4 rad = m.rad[path];
