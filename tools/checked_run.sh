@@ -8,7 +8,7 @@
 O=${1:-gpurun_out/checked_r2.txt}; mkdir -p "$(dirname $O)"
 [ -f build/ab/libmcpt_checked.so ] || bash tools/build_variant.sh checked -DMCPT_CHECKED=1 > /dev/null || exit 1
 echo "checked build (MCPT_CHECKED=1) on $(nvidia-smi --query-gpu=name --format=csv,noheader | head -1)" > $O
-for t in treelet lbvh fasttree wave chain mis merge stage metrics; do
+for t in treelet lbvh fasttree wave sorted chain mis merge stage metrics; do
 	MCPT_LIB=build/ab/libmcpt_checked.so timeout 600 python tools/sanitize_targets.py $t 1.0 >> $O 2>&1 || echo "target $t FAILED rc=$?" >> $O
 done
 echo "--- determinism stress (product build)" >> $O

@@ -99,6 +99,28 @@ def main(target, scale):
                 for trav in (device.TRAVERSAL_REFERENCE, device.TRAVERSAL_CANONICAL):
                     _, c3 = a.trace(rays, traversal=trav)
                     assert np.array_equal(c1, c3)
+    elif target == "sorted":
+        # coherence-sorted queues (waves of >= 2^18 paths): reference mode and NEE + MIS, including sort sizes estimated
+        # under another camera (the walk's sorted-prefix guard) - each against the unsorted pipeline
+        sc = scenes.load("cbox")
+        w = h = 512
+        kw = dict(seed_mode=1, run_seed=3, samples_in_flight=2)
+        away = sc.camera.copy()
+        away["direction"][0][:3] = -away["direction"][0][:3]
+        for sampling in (0, 1):
+            os.environ.pop("MCPT_SORT", None)
+            with ctx_for(sc, w, h, sampling=sampling, **kw) as a:
+                a.set_camera(away)
+                a.render(6)
+                a.set_camera(sc.camera)
+                a.reset_accumulation()
+                a.render(8)
+                got = a.read_sums().tobytes()
+            os.environ["MCPT_SORT"] = "0"
+            with ctx_for(sc, w, h, sampling=sampling, **kw) as b:
+                b.render(8)
+                assert got == b.read_sums().tobytes()
+        os.environ.pop("MCPT_SORT", None)
     elif target == "metrics":
         sc = scenes.load("veach_mis")
         q = device.bvh_metrics(sc.nodes, sc.triangles, sc.camera, 64, 48)
