@@ -182,6 +182,8 @@ struct mcpt_ctx {
 	// coherence order of the bounce queues (mcpt_kernels.cuh): keys written by the shade kernel, sorted by CUB, the
 	// resulting permutation read by the next walk
 	bool sort_queues = true;               // env MCPT_SORT=0 switches it off (A/B)
+	int shade_grid = 32;                   // blocks per SM of the shade kernels' grid-stride launches: 8 -> 32 measured +2.6 % on diningroom, +1.1 % cbox,
+	                                       // +1.4 % veach_mis (4 blocks are resident; finer blocks even out the tail; profiles/r3w_shade_grid.log; env MCPT_SHADE_GRID for A/B)
 	int mis_sort_mask = 3;                 // NEE + MIS: bit 0 main queue, bit 1 shadow queue (env MCPT_SORT=1/2/3)
 	// NEE + MIS: whether the two sorts pay depends on the scene (+13 % cbox, +14 % diningroom, -9 % veach_mis), and the
 	// image does not depend on the queue order, so one wave is timed each way and the faster arrangement kept.
@@ -438,7 +440,7 @@ int enqueue_wave(mcpt_ctx* c, int nsamples) {
 					c->ev_used += 2;
 					timed = true;
 				}
-				k_wave_shade<<<std::min(blocks(total, 256), c->nsm * 8), 256, 0, c->stream>>>(c->scene, w, d, D, c->prm.seed_mode);
+				k_wave_shade<<<std::min(blocks(total, 256), c->nsm * c->shade_grid), 256, 0, c->stream>>>(c->scene, w, d, D, c->prm.seed_mode);
 				++c->launches;
 				if (w.sort_keys) {
 					// the next bounce's walk order: live items first (their keys are fresh), sorted by coherence key
@@ -624,7 +626,7 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 	k_wave_generate<<<blocks(total, 256), 256, 0, c->stream>>>(c->cam, w, nsamples, c->prm.seed_mode, c->prm.run_seed);
 	const int BS = 128;
 	const int pg = std::min(blocks(total, BS), c->persistent_grid(BS));
-	const int sg = std::min(blocks(total, 256), c->nsm * 8);
+	const int sg = std::min(blocks(total, 256), c->nsm * c->shade_grid);
 	// coherence-sorted queues as in enqueue_wave: the main queue of the next bounce and this bounce's shadow-ray queue
 	const bool sorted = c->sort_queues && c->sort_keys.p && c->mis_skeys.p && size_t(total) <= c->sort_keys.n && total >= (1L << 18);
 	if (sorted) poll_live_counts(c);
@@ -771,6 +773,7 @@ mcpt_ctx* mcpt_create(const mcpt_params* params) {
 	if (const char* e = std::getenv("MCPT_OPT")) c->opt_flags = std::atoi(e);
 	if (const char* e = std::getenv("MCPT_BLOCK")) { int b = std::atoi(e); if (b == 64 || b == 128) c->block = b; }
 	if (const char* e = std::getenv("MCPT_SORT")) { c->sort_queues = std::atoi(e) != 0; if (c->sort_queues) c->mis_sort_mask = std::atoi(e) & 3; c->mis_sort_tune = false; }      // development A/B
+	if (const char* e = std::getenv("MCPT_SHADE_GRID")) c->shade_grid = std::max(1, std::min(1 << 16, std::atoi(e)));
 	if (const char* e = std::getenv("MCPT_HOST_TREE")) c->host_tree = std::atoi(e) != 0;
 	const size_t n = size_t(c->npix);
 	bool ok = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) == cudaSuccess;

@@ -526,6 +526,8 @@ __global__ void __launch_bounds__(128, MCPT_MIN_BLOCKS) k_wave_trace_persistent(
 	persistent_walk(sc, tmin, total, head, job);
 }
 
+// (62 registers: 4 blocks per SM.  Launch bounds for 5 / 6 blocks - 48 / 40 registers, 16 / 64 B of spills - measured
+// -1 % / -3 %, profiles/r3v_shade_variants.log.)
 __global__ void __launch_bounds__(256) k_wave_shade(SceneDev sc, WaveDev w, int depth, int max_depth, int seed_mode) {
 	const int src = depth & 1, dst = src ^ 1;
 	const uint32_t total = w.qcount[depth];
