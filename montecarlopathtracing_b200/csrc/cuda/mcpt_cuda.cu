@@ -187,7 +187,7 @@ struct mcpt_ctx {
 	int mis_sort_mask = 3;                 // NEE + MIS: bit 0 main queue, bit 1 shadow queue (env MCPT_SORT=1/2/3)
 	// NEE + MIS: whether the two sorts pay depends on the scene (+13 % cbox, +14 % diningroom, -9 % veach_mis), and the
 	// image does not depend on the queue order, so one wave is timed each way and the faster arrangement kept.
-	struct SortTrial { cudaEvent_t t0 = nullptr, t1 = nullptr; bool pending = false, have = false; double ms_per_path = 0.0; } mis_trial[2];
+	struct SortTrial { cudaEvent_t t0 = nullptr, t1 = nullptr; bool pending = false, have = false; double paths = 0.0, ms_per_path = 0.0; } mis_trial[2];
 	int mis_sort_choice = -1;              // -1 undecided; else the mask in force until the scene or the camera changes
 	bool mis_sort_tune = true;             // off when MCPT_SORT pins the mask
 	bool host_tree = false;                // env MCPT_HOST_TREE=1: the fast walk's tree from the host builder instead of sah_build.cu (same bytes)
@@ -638,7 +638,7 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 				if (!t.pending || cudaEventQuery(t.t1) != cudaSuccess) continue;
 				float ms = 0.0f;
 				CU(cudaEventElapsedTime(&ms, t.t0, t.t1));
-				t.pending = false; t.have = true; t.ms_per_path = double(ms) / t.ms_per_path;
+				t.pending = false; t.have = true; t.ms_per_path = double(ms) / t.paths;
 			}
 			(void)cudaGetLastError();
 			if (c->mis_trial[0].have && c->mis_trial[1].have) c->mis_sort_choice = c->mis_trial[0].ms_per_path <= c->mis_trial[1].ms_per_path ? 3 : 0;
@@ -678,14 +678,15 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 				CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->mis_skeys.p, c->sort_keys_out.p, c->sort_iota.p,
 				                                   c->mis_sperm.p, int(ns), 0, SORT_KEY_BITS, c->stream));
 				sperm = c->mis_sperm.p;
+				c->launches += 5;       // CUB's histogram, exclusive sum and 3 onesweep passes
 			}
 			if (m.keys) {
 				k_invalidate_keys<<<c->nsm * 2, 256, 0, c->stream>>>(c->sort_keys.p, c->qcount.p + d + 1, c->qcount.p + d);
 				CU(cub::DeviceRadixSort::SortPairs(c->sort_temp.p, c->sort_temp_bytes, c->sort_keys.p, c->sort_keys_out.p, c->sort_iota.p,
 				                                   c->sort_perm.p, int(estimate(d + 1)), 0, SORT_KEY_BITS, c->stream));
 				perm_n = uint32_t(estimate(d + 1));
+				c->launches += 6;
 			}
-			c->launches += 12;
 		}
 		k_trace_queue_persistent<<<pg, BS, 0, c->stream>>>(c->scene, m.sod, m.sdp, m.shit, c->mis_scount.p + d, c->prm.tmin, c->mis_shead.p + d, sperm, uint32_t(ns));
 		k_wave_nee_add<<<sg, 256, 0, c->stream>>>(m, d);
@@ -695,7 +696,7 @@ int enqueue_wave_mis(mcpt_ctx* c, int nsamples) {
 		auto& t = c->mis_trial[trial];
 		CU(cudaEventRecord(t.t1, c->stream));
 		t.pending = true;
-		t.ms_per_path = double(total);       // divisor until the time arrives
+		t.paths = double(total);
 	}
 	if (sorted)
 		if (int r = record_live_counts(c, total)) return r;
